@@ -1,0 +1,111 @@
+"""correlation(input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, padding)
+
+Drop-in for the reference's ``src/correlation.py:7-14`` (forward) and ``:17-35`` (registered gradient), on NHWC
+float32 CUDA tensors.  Shape and error behaviour follow ``src/ops/correlation/correlation_op.cc:9-62`` and
+``correlation_kernel.cc:23-53``.
+"""
+import ctypes
+import os
+
+import torch
+
+from . import _lib
+
+#: arithmetic of the contraction when the caller does not pass ``precision=``: "fp32" (default; matches the
+#: reference within 1e-5 rel / 1e-6 abs), "tf32", "bf16" or "tf32x3".  Override with FN2_CORR_PRECISION.
+DEFAULT_PRECISION = os.environ.get("FN2_CORR_PRECISION", "fp32")
+
+
+def _prec(precision):
+    p = DEFAULT_PRECISION if precision is None else precision
+    if p not in _lib.PRECISIONS:
+        raise ValueError("precision must be one of %s" % sorted(_lib.PRECISIONS))
+    return _lib.PRECISIONS[p]
+
+
+def output_shape(H, W, kernel_size, max_displacement, stride_1, stride_2, padding):
+    """[out_h, out_w, out_channels] -- the op's shape function (correlation_op.cc:9-51)."""
+    oh, ow, oc = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    st = _lib.lib().fn2_correlation_output_shape(H, W, kernel_size, max_displacement, stride_1, stride_2, padding,
+                                                 ctypes.byref(oh), ctypes.byref(ow), ctypes.byref(oc))
+    _lib.check(st, "Correlation")
+    return oh.value, ow.value, oc.value
+
+
+def _check_pair(a, b):
+    _lib.require_cuda_f32(a, "input_a")
+    _lib.require_cuda_f32(b, "input_b")
+    if a.shape != b.shape:  # shape fn merges the two input shapes (correlation_op.cc:17)
+        raise ValueError("input_a and input_b must have the same shape, got %s and %s"
+                         % (tuple(a.shape), tuple(b.shape)))
+    if a.device != b.device:
+        raise ValueError("input_a and input_b must be on the same device")
+
+
+def _workspace(a, geom, prec, direction):
+    nbytes = _lib.lib().fn2_correlation_workspace_bytes(*geom, prec, direction)
+    if nbytes == 0:
+        return None, 0, ctypes.c_void_p(0)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=a.device)
+    return ws, nbytes, ctypes.c_void_p(ws.data_ptr())
+
+
+def _forward(a, b, k, md, s1, s2, pad, prec):
+    _check_pair(a, b)
+    N, H, W, C = a.shape
+    oh, ow, oc = output_shape(H, W, k, md, s1, s2, pad)
+    out = torch.empty((N, oh, ow, oc), dtype=torch.float32, device=a.device)
+    geom = (N, H, W, C, k, md, s1, s2, pad)
+    with torch.cuda.device(a.device):
+        ws, nbytes, wsp = _workspace(a, geom, prec, 0)
+        st = _lib.lib().fn2_correlation_forward(a.data_ptr(), b.data_ptr(), out.data_ptr(), *geom, prec, wsp, nbytes,
+                                                _lib.current_stream_ptr(a.device))
+    _lib.check(st, "Correlation")
+    return out
+
+
+def correlation_grad(gradients, input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, pad,
+                     precision=None):
+    """The ``CorrelationGrad`` op (correlation_op.cc:64-82): returns (backprops_a, backprops_b)."""
+    prec = _prec(precision)
+    _check_pair(input_a, input_b)
+    _lib.require_cuda_f32(gradients, "gradients")
+    N, H, W, C = input_a.shape
+    oh, ow, oc = output_shape(H, W, kernel_size, max_displacement, stride_1, stride_2, pad)
+    if tuple(gradients.shape) != (N, oh, ow, oc):
+        raise ValueError("gradients must have shape %s, got %s" % ((N, oh, ow, oc), tuple(gradients.shape)))
+    ga = torch.empty_like(input_a)
+    gb = torch.empty_like(input_b)
+    geom = (N, H, W, C, kernel_size, max_displacement, stride_1, stride_2, pad)
+    with torch.cuda.device(input_a.device):
+        ws, nbytes, wsp = _workspace(input_a, geom, prec, 1)
+        st = _lib.lib().fn2_correlation_backward(gradients.data_ptr(), input_a.data_ptr(), input_b.data_ptr(),
+                                                 ga.data_ptr(), gb.data_ptr(), *geom, prec, wsp, nbytes,
+                                                 _lib.current_stream_ptr(input_a.device))
+    _lib.check(st, "CorrelationGrad")
+    return ga, gb
+
+
+class _Correlation(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b, k, md, s1, s2, pad, prec):
+        ctx.save_for_backward(a, b)
+        ctx.attrs = (k, md, s1, s2, pad, prec)
+        return _forward(a, b, k, md, s1, s2, pad, prec)
+
+    @staticmethod
+    def backward(ctx, gradients):
+        a, b = ctx.saved_tensors
+        k, md, s1, s2, pad, prec = ctx.attrs
+        names = {v: n for n, v in _lib.PRECISIONS.items()}
+        ga, gb = correlation_grad(gradients.contiguous(), a, b, k, md, s1, s2, pad, precision=names[prec])
+        return ga, gb, None, None, None, None, None, None
+
+
+def correlation(input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, padding, *, precision=None):
+    """Cost volume between two feature maps; same positional signature as the reference wrapper.
+
+    ``precision`` is the one keyword-only extension: "fp32" (default), "tf32", "bf16", "tf32x3".
+    """
+    args = [int(v) for v in (kernel_size, max_displacement, stride_1, stride_2, padding)]
+    return _Correlation.apply(input_a, input_b, *args, _prec(precision))

@@ -1,0 +1,165 @@
+// fn2_api.cu -- the C ABI of libfn2ops.so (include/fn2ops.h): argument validation mirroring each OP_REQUIRES of the
+// reference OpKernels, then dispatch to the sm_100a kernels.  No allocation, no host synchronisation.
+#include <atomic>
+#include <cmath>
+#include "fn2_common.cuh"
+
+namespace fn2 {
+
+static std::atomic<unsigned long long> g_launches{0};
+static thread_local int t_last_cuda_error = 0;
+
+void note_cuda_error(cudaError_t e) { t_last_cuda_error = (int)e; }
+
+int after_launch() {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    note_cuda_error(e);
+    return FN2_E_CUDA;
+  }
+  return FN2_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// correlation_kernel.cc:23,35-57 (+ the shape fn correlation_op.cc:9-51)
+static int make_geom(int N, int H, int W, int C, int k, int md, int s1, int s2, int pad, CorrGeom* g) {
+  if (N < 1 || H < 1 || W < 1 || C < 1) return FN2_E_BAD_SHAPE;
+  if (k < 1 || md < 0 || s1 < 1 || s2 < 1 || pad < 0) return FN2_E_BAD_PARAM;
+  if (k % 2 == 0) return FN2_E_KERNEL_SIZE_EVEN;
+  g->N = N; g->H = H; g->W = W; g->C = C;
+  g->k = k; g->md = md; g->s1 = s1; g->s2 = s2; g->pad = pad;
+  g->kr = (k - 1) / 2;
+  const int border = md + g->kr;
+  const int pH = H + 2 * pad, pW = W + 2 * pad;
+  g->oH = (int)std::ceil((float)(pH - border * 2) / (float)s1);
+  g->oW = (int)std::ceil((float)(pW - border * 2) / (float)s1);
+  if (g->oH < 1) return FN2_E_OUT_HEIGHT;
+  if (g->oW < 1) return FN2_E_OUT_WIDTH;
+  g->r = md / s2;
+  g->gw = g->r * 2 + 1;
+  g->D = g->gw * g->gw;
+  g->off = md - pad;
+  return FN2_OK;
+}
+
+}  // namespace fn2
+
+using namespace fn2;
+
+extern "C" {
+
+int fn2_abi_version(void) { return FN2_ABI_VERSION; }
+
+const char* fn2_error_string(int status) {
+  switch (status) {
+    case FN2_OK: return "ok";
+    case FN2_E_KERNEL_SIZE_EVEN: return "kernel_size must be odd";
+    case FN2_E_OUT_HEIGHT: return "Neighborhood and kernel don't fit in input height.";
+    case FN2_E_OUT_WIDTH: return "Neighborhood and kernel don't fit in input width.";
+    case FN2_E_BAD_SHAPE: return "tensor dimensions must be >= 1 and consistent (rank-4 NHWC)";
+    case FN2_E_BAD_PARAM: return "stride_1/stride_2 must be >= 1, kernel_size >= 1, max_displacement and pad >= 0";
+    case FN2_E_BAD_POINTER: return "null or misaligned device pointer (16-byte alignment required)";
+    case FN2_E_UNSUPPORTED_PRECISION: return "precision not supported for these arguments";
+    case FN2_E_WORKSPACE: return "workspace too small; see fn2_correlation_workspace_bytes";
+    case FN2_E_DOWNSAMPLE_SIZE: return "downsample output height and width must be >= 2";
+    case FN2_E_CUDA: return "CUDA error; see fn2_last_cuda_error";
+    case FN2_E_NO_DEVICE: return "no sm_100 CUDA device is current";
+    default: return "unknown fn2 status";
+  }
+}
+
+int fn2_last_cuda_error(void) { return t_last_cuda_error; }
+
+unsigned long long fn2_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int fn2_correlation_output_shape(int H, int W, int k, int md, int s1, int s2, int pad, int* oh, int* ow, int* oc) {
+  CorrGeom g;
+  const int rc = make_geom(1, H, W, 1, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (oh) *oh = g.oH;
+  if (ow) *ow = g.oW;
+  if (oc) *oc = g.D;
+  return FN2_OK;
+}
+
+size_t fn2_correlation_workspace_bytes(int N, int H, int W, int C, int k, int md, int s1, int s2, int pad,
+                                       int precision, int direction) {
+  CorrGeom g;
+  if (make_geom(N, H, W, C, k, md, s1, s2, pad, &g) != FN2_OK) return 0;
+  if (precision == FN2_PREC_FP32) return 0;
+  if (!corr_tc_supported(g, precision)) return 0;
+  return corr_tc_workspace_bytes(g, precision, direction);
+}
+
+int fn2_correlation_forward(const float* a, const float* b, float* out, int N, int H, int W, int C, int k, int md,
+                            int s1, int s2, int pad, int precision, void* ws, size_t ws_bytes, void* stream) {
+  CorrGeom g;
+  const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (!a || !b || !out || !aligned16(a) || !aligned16(b) || !aligned16(out)) return FN2_E_BAD_POINTER;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (precision) {
+    case FN2_PREC_FP32:
+      if (corr_simt_supported(g)) return corr_simt_forward(g, a, b, out, st);
+      return corr_generic_forward(g, a, b, out, st);
+    case FN2_PREC_TF32:
+    case FN2_PREC_BF16:
+    case FN2_PREC_TF32X3:
+      if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+      if (ws_bytes < corr_tc_workspace_bytes(g, precision, 0) || (ws_bytes && !ws)) return FN2_E_WORKSPACE;
+      return corr_tc_forward(g, a, b, out, precision, ws, ws_bytes, st);
+    default:
+      return FN2_E_UNSUPPORTED_PRECISION;
+  }
+}
+
+int fn2_correlation_backward(const float* gout, const float* a, const float* b, float* ga, float* gb, int N, int H,
+                             int W, int C, int k, int md, int s1, int s2, int pad, int precision, void* ws,
+                             size_t ws_bytes, void* stream) {
+  CorrGeom g;
+  const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (!gout || !a || !b || !ga || !gb) return FN2_E_BAD_POINTER;
+  if (!aligned16(gout) || !aligned16(a) || !aligned16(b) || !aligned16(ga) || !aligned16(gb)) return FN2_E_BAD_POINTER;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (precision) {
+    case FN2_PREC_FP32:
+      if (corr_simt_supported(g)) return corr_simt_backward(g, gout, a, b, ga, gb, st);
+      return corr_generic_backward(g, gout, a, b, ga, gb, st);
+    case FN2_PREC_TF32:
+    case FN2_PREC_BF16:
+    case FN2_PREC_TF32X3:
+      if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+      if (ws_bytes < corr_tc_workspace_bytes(g, precision, 1) || (ws_bytes && !ws)) return FN2_E_WORKSPACE;
+      return corr_tc_backward(g, gout, a, b, ga, gb, precision, ws, ws_bytes, st);
+    default:
+      return FN2_E_UNSUPPORTED_PRECISION;
+  }
+}
+
+int fn2_flow_warp_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
+                          void* stream) {
+  if (N < 1 || H < 1 || W < 1 || C < 1) return FN2_E_BAD_SHAPE;
+  if (!image || !flow || !out || !aligned16(image) || !aligned16(flow) || !aligned16(out)) return FN2_E_BAD_POINTER;
+  return flow_warp_forward(image, flow, out, N, H, W, C, static_cast<cudaStream_t>(stream));
+}
+
+int fn2_flow_warp_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
+                           int N, int H, int W, int C, void* stream) {
+  if (N < 1 || H < 1 || W < 1 || C < 1) return FN2_E_BAD_SHAPE;
+  if (!image || !flow || !gout || !gimage || !gflow) return FN2_E_BAD_POINTER;
+  if (!aligned16(image) || !aligned16(flow) || !aligned16(gout) || !aligned16(gimage) || !aligned16(gflow))
+    return FN2_E_BAD_POINTER;
+  return flow_warp_backward(image, flow, gout, gimage, gflow, N, H, W, C, static_cast<cudaStream_t>(stream));
+}
+
+int fn2_downsample_forward(const float* in, float* out, int N, int iH, int iW, int C, int oH, int oW, void* stream) {
+  if (N < 1 || iH < 1 || iW < 1 || C < 1 || oH < 1 || oW < 1) return FN2_E_BAD_SHAPE;
+  if (oH < 2 || oW < 2) return FN2_E_DOWNSAMPLE_SIZE;
+  if (!in || !out || !aligned16(in) || !aligned16(out)) return FN2_E_BAD_POINTER;
+  return downsample_forward(in, out, N, iH, iW, C, oH, oW, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,62 @@
+// fn2_common.cuh -- shared declarations for libfn2ops.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/fn2ops.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libfn2ops is written for sm_100a (B200) only"
+#endif
+
+namespace fn2 {
+
+// Geometry of one correlation call, derived exactly as correlation_kernel.cc:35-57 does.
+struct CorrGeom {
+  int N, H, W, C;
+  int k, md, s1, s2, pad;
+  int kr, oH, oW, r, gw, D;
+  int off;  // unpadded coordinate of output (0,0)'s patch corner: md - pad
+};
+
+// Records a launch for fn2_launch_count() and returns the status of the launch that was just made.
+int after_launch();
+void note_cuda_error(cudaError_t e);
+
+// ---- kernels (one translation unit each) ------------------------------------------------------------------
+int corr_generic_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st);
+int corr_generic_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
+                          float* gb, cudaStream_t st);
+
+// fp32 CUDA-core kernels for kernel_size == 1, stride_1 == 1 (the FlowNetC call, flownet_c.py:40)
+bool corr_simt_supported(const CorrGeom& g);
+int corr_simt_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st);
+int corr_simt_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
+                       cudaStream_t st);
+
+// tcgen05 kernels (tf32 / 3xTF32 / bf16)
+bool corr_tc_supported(const CorrGeom& g, int precision);
+size_t corr_tc_workspace_bytes(const CorrGeom& g, int precision, int direction);
+int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void* ws,
+                    size_t ws_bytes, cudaStream_t st);
+int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
+                     int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+
+int flow_warp_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
+                      cudaStream_t st);
+int flow_warp_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow, int N,
+                       int H, int W, int C, cudaStream_t st);
+int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C, int oH, int oW, cudaStream_t st);
+
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+// floor / ceil division for possibly negative numerators (b > 0)
+__host__ __device__ inline int floor_div(int a, int b) {
+  int q = a / b, r = a % b;
+  return q - ((r != 0) && (r < 0));
+}
+__host__ __device__ inline int ceil_div_s(int a, int b) {
+  int q = a / b, r = a % b;
+  return q + ((r != 0) && (r > 0));
+}
+
+}  // namespace fn2

@@ -1,0 +1,44 @@
+"""downsample(tensor, size) -- drop-in for the reference's ``src/downsample.py:7-8``.
+
+``size`` = [out_height, out_width] (the op attr, ``src/ops/downsample/downsample_op.cc:24-28``).  The reference
+registers no gradient for this op; differentiating through it raises LookupError here as tf.gradients does there.
+"""
+import torch
+
+from . import _lib
+
+
+def _forward(tensor, size):
+    _lib.require_cuda_f32(tensor, "input")  # "Input images must have rank 4" (downsample_kernel.cc:25)
+    size = list(size)
+    if len(size) != 2:  # downsample_kernel.cc:19
+        raise ValueError("size must be 2 dimensions")
+    oh, ow = int(size[0]), int(size[1])
+    N, H, W, C = tensor.shape
+    if oh < 1 or ow < 1:
+        raise ValueError("Downsample: output dimensions must be positive")
+    out = torch.empty((N, oh, ow, C), dtype=torch.float32, device=tensor.device)
+    with torch.cuda.device(tensor.device):
+        st = _lib.lib().fn2_downsample_forward(tensor.data_ptr(), out.data_ptr(), N, H, W, C, oh, ow,
+                                               _lib.current_stream_ptr(tensor.device))
+    _lib.check(st, "Downsample")
+    return out
+
+
+class _Downsample(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tensor, oh, ow):
+        return _forward(tensor, (oh, ow))
+
+    @staticmethod
+    def backward(ctx, gradients):
+        raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
+
+
+def downsample(tensor, size):
+    size = list(size)
+    if len(size) != 2:
+        raise ValueError("size must be 2 dimensions")
+    if isinstance(tensor, torch.Tensor) and tensor.requires_grad:
+        return _Downsample.apply(tensor, int(size[0]), int(size[1]))
+    return _forward(tensor, size)

@@ -1,0 +1,62 @@
+"""flow_warp(image, flow) -- drop-in for the reference's ``src/flow_warp.py:7-8`` and its gradient ``:11-15``.
+
+Shapes per ``src/ops/flow_warp/flow_warp_op.cc:6-22``; validation per ``flow_warp.cc:22-31``.
+"""
+import torch
+
+from . import _lib
+
+
+def _check(image, flow):
+    _lib.require_cuda_f32(image, "image")  # "Input images must have rank 4"
+    _lib.require_cuda_f32(flow, "flow")    # "Input flow must have rank 4"
+    if image.shape[:3] != flow.shape[:3]:  # flow_warp.cc:26-31
+        raise ValueError("Input images and flows must have the same batch size, height and width")
+    if flow.shape[3] != 2:
+        raise ValueError("flow must have 2 channels")
+    if image.device != flow.device:
+        raise ValueError("image and flow must be on the same device")
+
+
+def _forward(image, flow):
+    _check(image, flow)
+    N, H, W, C = image.shape
+    out = torch.empty_like(image)
+    with torch.cuda.device(image.device):
+        st = _lib.lib().fn2_flow_warp_forward(image.data_ptr(), flow.data_ptr(), out.data_ptr(), N, H, W, C,
+                                              _lib.current_stream_ptr(image.device))
+    _lib.check(st, "FlowWarp")
+    return out
+
+
+def flow_warp_grad(image, flow, gradients):
+    """The ``FlowWarpGrad`` op with both declared outputs (flow_warp_op.cc:13-22): (image_grad, flow_grad)."""
+    _check(image, flow)
+    _lib.require_cuda_f32(gradients, "gradients")
+    if gradients.shape != image.shape:
+        raise ValueError("gradients must have the shape of image")
+    N, H, W, C = image.shape
+    gimage = torch.empty_like(image)  # zero-filled by the library on the same stream
+    gflow = torch.empty_like(flow)
+    with torch.cuda.device(image.device):
+        st = _lib.lib().fn2_flow_warp_backward(image.data_ptr(), flow.data_ptr(), gradients.data_ptr(),
+                                               gimage.data_ptr(), gflow.data_ptr(), N, H, W, C,
+                                               _lib.current_stream_ptr(image.device))
+    _lib.check(st, "FlowWarpGrad")
+    return gimage, gflow
+
+
+class _FlowWarp(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, image, flow):
+        ctx.save_for_backward(image, flow)
+        return _forward(image, flow)
+
+    @staticmethod
+    def backward(ctx, gradients):
+        image, flow = ctx.saved_tensors
+        return flow_warp_grad(image, flow, gradients.contiguous())
+
+
+def flow_warp(image, flow):
+    return _FlowWarp.apply(image, flow)

@@ -1,0 +1,126 @@
+/*
+ * fn2ops.h -- C ABI of libfn2ops.so: the B200 (sm_100a) replacement for the three TensorFlow custom-op
+ * libraries of fperezgamonal/flownet2-tf (correlation.so, flow_warp.so, downsample.so).
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the reference repo).  The
+ * reference binds its ops with tf.load_op_library + OpKernel::Compute; this library is bound with ctypes (see
+ * INTEGRATION.md for the stub a maintainer adds to src/correlation.py, src/flow_warp.py, src/downsample.py).
+ *
+ * Conventions
+ *   - All tensors are NHWC, contiguous, float32, resident in device memory of the current CUDA device.
+ *   - The caller owns every buffer (inputs, outputs, workspace).  The library allocates nothing, keeps no
+ *     pointer after returning, and fully defines every output element (no pre-zeroing needed).
+ *   - Every call only enqueues work on `stream` (a cudaStream_t passed as void*; NULL = legacy default
+ *     stream) and returns without synchronising; calls are re-entrant and CUDA-graph capturable.
+ *   - Return value: FN2_OK (0) or a negative fn2_status.  Nothing throws, prints or exits.
+ *   - Element counts above 2^31 are supported (64-bit indexing); each single dimension must fit in int.
+ */
+#ifndef FN2OPS_H_
+#define FN2OPS_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FN2_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define FN2_API __attribute__((visibility("default")))
+#else
+#define FN2_API
+#endif
+
+typedef enum fn2_status {
+  FN2_OK = 0,
+  FN2_E_KERNEL_SIZE_EVEN = -1, /* "kernel_size must be odd"            correlation_kernel.cc:23            */
+  FN2_E_OUT_HEIGHT = -2,       /* "Neighborhood and kernel don't fit in input height."  correlation_kernel.cc:50 */
+  FN2_E_OUT_WIDTH = -3,        /* "Neighborhood and kernel don't fit in input width."   correlation_kernel.cc:52 */
+  FN2_E_BAD_SHAPE = -4,        /* a dimension < 1, or shapes that the op's shape fn would reject         */
+  FN2_E_BAD_PARAM = -5,        /* stride < 1, max_displacement < 0, pad < 0                              */
+  FN2_E_BAD_POINTER = -6,      /* NULL or misaligned (float32 tensors must be 16-byte aligned)           */
+  FN2_E_UNSUPPORTED_PRECISION = -7,
+  FN2_E_WORKSPACE = -8,        /* workspace smaller than fn2_correlation_workspace_bytes()              */
+  FN2_E_DOWNSAMPLE_SIZE = -9,  /* output height or width < 2: the reference divides by zero there
+                                  (downsample_kernel_gpu.cu.cc:40-41,92-93); rejected instead           */
+  FN2_E_CUDA = -10,            /* a CUDA runtime/driver call failed; see fn2_last_cuda_error()          */
+  FN2_E_NO_DEVICE = -11        /* no sm_100 device is current                                           */
+} fn2_status;
+
+/* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode. */
+typedef enum fn2_precision {
+  FN2_PREC_FP32 = 0,   /* fp32 FMA on the CUDA cores; matches the reference within 1e-5 rel / 1e-6 abs      */
+  FN2_PREC_TF32 = 1,   /* tcgen05 kind::tf32, fp32 accumulate in TMEM                                      */
+  FN2_PREC_BF16 = 2,   /* tcgen05 kind::f16 (bf16 operands), fp32 accumulate in TMEM                       */
+  FN2_PREC_TF32X3 = 3  /* tcgen05 3xTF32 split (hi*hi + hi*lo + lo*hi): fp32-grade result on tensor cores   */
+} fn2_precision;
+
+FN2_API int fn2_abi_version(void);
+FN2_API const char* fn2_error_string(int status);
+/* cudaError_t of the last failing CUDA call made by this thread through the library (0 if none). */
+FN2_API int fn2_last_cuda_error(void);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Correlation.  Replaces REGISTER_OP("Correlation") + CorrelationKernel<GPUDevice>::Compute
+ * (src/ops/correlation/correlation_op.cc:9-62, correlation_kernel.cc:13-136) and the Pad/CorrelateData
+ * launchers beneath it (pad.cu.cc:46-74, correlation_kernel.cu.cc:121-150).  No padded temporaries are made.
+ *
+ *   out[n,yo,xo,(p+r)*gw+(o+r)] = 1/(k*k*C) * sum_{j,i<k} sum_c  A[n, yo*s1+md+j,      xo*s1+md+i,      c]
+ *                                                              * B[n, yo*s1+md+j+s2*p, xo*s1+md+i+s2*o, c]
+ *   with A,B = a,b zero-padded by `pad`, r = md / s2 (integer), gw = 2r+1, p,o in [-r, r].
+ * --------------------------------------------------------------------------------------------------------- */
+
+/* Shape function (correlation_op.cc:9-51, correlation_kernel.cc:35-57): out = [N, *out_h, *out_w, *out_c]. */
+FN2_API int fn2_correlation_output_shape(int H, int W, int kernel_size, int max_displacement, int stride_1, int stride_2,
+                                 int pad, int* out_h, int* out_w, int* out_c);
+
+/* Scratch bytes needed by the chosen precision (0 for FN2_PREC_FP32).  direction: 0 = forward, 1 = backward. */
+FN2_API size_t fn2_correlation_workspace_bytes(int N, int H, int W, int C, int kernel_size, int max_displacement,
+                                       int stride_1, int stride_2, int pad, int precision, int direction);
+
+FN2_API int fn2_correlation_forward(const float* input_a, const float* input_b, float* output, int N, int H, int W, int C,
+                            int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
+                            int precision, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Replaces REGISTER_OP("CorrelationGrad") + CorrelationGradKernel<GPUDevice>::Compute
+ * (correlation_op.cc:64-82, correlation_grad_kernel.cc:15-159) and CorrelationGradA/B
+ * (correlation_grad_kernel.cu.cc:191-259).  One launch set for the whole batch; no atomics; both gradients
+ * are fully written. */
+FN2_API int fn2_correlation_backward(const float* gradients, const float* input_a, const float* input_b, float* backprops_a,
+                             float* backprops_b, int N, int H, int W, int C, int kernel_size, int max_displacement,
+                             int stride_1, int stride_2, int pad, int precision, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * FlowWarp.  Replaces REGISTER_OP("FlowWarp") + FlowWarpKernel<GPUDevice>::Compute
+ * (src/ops/flow_warp/flow_warp_op.cc:6-11, flow_warp.cc:13-47, launcher flow_warp.cu.cc:99-127).
+ * image [N,H,W,C], flow [N,H,W,2] (channel 0 = x, 1 = y), output [N,H,W,C].
+ * --------------------------------------------------------------------------------------------------------- */
+FN2_API int fn2_flow_warp_forward(const float* image, const float* flow, float* output, int N, int H, int W, int C,
+                          void* stream);
+
+/* Replaces REGISTER_OP("FlowWarpGrad") + FlowWarpGradKernel<GPUDevice>::Compute
+ * (flow_warp_op.cc:13-22, flow_warp_grad.cc:13-56, launcher flow_warp_grad.cu.cc:90-123) with the two outputs the
+ * op declares (the reference allocates both at index 0, flow_warp_grad.cc:36-37, and so cannot run).
+ * image_grad is zero-filled inside, on `stream`.  image_grad accumulates with fp32 atomics: run-to-run results
+ * may differ in the last bits, exactly as in the reference. */
+FN2_API int fn2_flow_warp_backward(const float* image, const float* flow, const float* gradients, float* image_grad,
+                           float* flow_grad, int N, int H, int W, int C, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Downsample.  Replaces REGISTER_OP("Downsample") + DownsampleKernel<GPUDevice>::Compute
+ * (src/ops/downsample/downsample_op.cc:11-28, downsample_kernel.cc:13-46, launcher
+ * downsample_kernel_gpu.cu.cc:80-104).  input [N,in_h,in_w,C] -> output [N,out_h,out_w,C].
+ * --------------------------------------------------------------------------------------------------------- */
+FN2_API int fn2_downsample_forward(const float* input, float* output, int N, int in_h, int in_w, int C, int out_h,
+                           int out_w, void* stream);
+
+/* Number of kernel launches (library kernels, not memsets) enqueued by this process so far; bench.py reports the
+ * difference over its timed region as `gpu_launches`. */
+FN2_API unsigned long long fn2_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FN2OPS_H_ */
