@@ -97,10 +97,10 @@ def require_cuda_f32(t, name, rank=4):
         raise TypeError("%s must be a torch.Tensor" % name)
     if t.dim() != rank:
         raise ValueError("%s must have rank %d" % (name, rank))
-    if not t.is_cuda:
-        raise ValueError("%s must be a CUDA tensor (there is no CPU implementation of this op)" % name)
     if t.dtype != torch.float32:
         raise TypeError("%s must be float32" % name)
+    if not t.is_cuda:
+        raise ValueError("%s must be a CUDA tensor (there is no CPU implementation of this op)" % name)
     if not t.is_contiguous():
         raise ValueError("%s must be contiguous NHWC" % name)
     return t

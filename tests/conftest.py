@@ -1,0 +1,71 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with `-m gpu`)")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:  # pragma: no cover
+        has_gpu = False
+    if has_gpu:
+        return
+    skip = pytest.mark.skip(reason="no CUDA device")
+    for item in items:
+        if "gpu" in item.keywords:
+            item.add_marker(skip)
+
+
+# ---- shared synthetic inputs ----------------------------------------------------------
+def corr_inputs(N, H, W, C, seed=1234):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    a = torch.nn.functional.leaky_relu(torch.randn(N, H, W, C, generator=g), 0.1)
+    b = torch.nn.functional.leaky_relu(torch.randn(N, H, W, C, generator=g), 0.1)
+    return a.contiguous(), b.contiguous()
+
+
+def grad_like(shape, seed=1235):
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(*shape, generator=g)
+
+
+def warp_inputs(N, H, W, C=3, seed=1236):
+    """image in [0,1); flow ~ 8 px with 5 % far out of range, 1 % exactly integer, a few NaN."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    image = torch.rand(N, H, W, C, generator=g)
+    flow = torch.randn(N, H, W, 2, generator=g) * 8
+    u = torch.rand(N, H, W, generator=g)
+    far = u < 0.05
+    flow[far] = torch.where(torch.rand(int(far.sum()), 2, generator=g) < 0.5, -2.0 * W, 2.0 * W)
+    integer = (u >= 0.05) & (u < 0.06)
+    flow[integer] = flow[integer].round()
+    flow.view(-1, 2)[::max(1, (N * H * W) // 7)] = float("nan")
+    return image.contiguous(), flow.contiguous()
+
+
+def assert_close(got, want, rel=1e-5, abs_=1e-6, what=""):
+    """|got - want| <= abs_ + rel * |want| elementwise (the tolerance BASELINE.json's north_star states)."""
+    got = np.asarray(got, np.float64)
+    want = np.asarray(want, np.float64)
+    assert got.shape == want.shape, (got.shape, want.shape)
+    nan_g, nan_w = np.isnan(got), np.isnan(want)
+    assert (nan_g == nan_w).all(), "%s: NaN pattern differs" % what
+    err = np.abs(np.where(nan_w, 0, got - want))
+    lim = abs_ + rel * np.abs(np.where(nan_w, 0, want))
+    bad = err > lim
+    assert not bad.any(), "%s: %d/%d outside tolerance, max err %.3e (limit there %.3e)" % (
+        what, int(bad.sum()), bad.size, float(err.max()), float(lim.flat[int(err.argmax())]))
