@@ -1,8 +1,407 @@
-// corr_tc.cu -- tcgen05 correlation (placeholder: not yet enabled)
+// corr_tc.cu -- FlowNetC correlation on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), sm_100a.
+//
+// Formulation (kernel_size 1, stride_1 1, pad == max_displacement; the FlowNetC call, flownet_c.py:40):
+//   out[n,y,x,(p,o)] = 1/C * sum_c a[n,y,x,c] * b[n,y+s2*p,x+s2*o,c]
+// With stride_2 = 2 the displacements are even, so pixels only ever meet pixels of the same (y%2, x%2) parity class.
+// Inside one class the op is a stride-1 window correlation on the half-resolution grid: a banded Gram matrix
+//   S[pixel i of a, pixel j of b] = <a_i, b_j>,  needed where |yj-yi| <= r and |xj-xi| <= r.
+// One CTA owns an M = 128 tile of a-pixels (4 class-rows x 32 class-cols), keeps it resident in shared memory for the
+// full K = C (fp32, read by the tensor core as tf32: no conversion pass), and streams the b-rows it needs through a
+// TMA ring in blocks of 128 b-pixels x 32 channels.  Each block is one [128 x 128] accumulator in TMEM (4 buffers of
+// 128 columns), produced by C/8 tcgen05.mma (M128 N128 K8, kind::tf32) and drained by four epilogue warps that pick
+// the +-r window out of each TMEM row, restage it through shared memory and write the 441-channel output coalesced.
+// Zero padding is TMA out-of-bounds fill; b-rows outside the image are never loaded, their outputs are written as 0.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = epilogue.
+#include <cuda.h>
+#include <mutex>
 #include "fn2_common.cuh"
+
 namespace fn2 {
-bool corr_tc_supported(const CorrGeom&, int) { return false; }
+namespace {
+
+constexpr int TILE_R = 4;          // a-rows per tile (class space)
+constexpr int TILE_C = 32;         // a-cols per tile
+constexpr int KCH = 32;            // channels per K-chunk = one 128-byte swizzle row
+constexpr int BLK_N = 128;         // b-pixels per accumulator block
+constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 128 B
+constexpr int NSTAGE = 5;          // B ring depth
+constexpr int NBUF = 4;            // TMEM accumulator buffers (4 x 128 columns = 512)
+constexpr int MAX_KC = 8;          // C <= 256
+constexpr int NTHREADS = 192;
+
+struct TcParams {
+  CUtensorMap a[4];
+  CUtensorMap b[4];
+  float* out;
+  int N, H, W, C, D, s2, ncls;
+  int Hc[2], Wc[2];   // class-space extent per parity
+  int TY, TX;         // tiles per class (upper bound over classes)
+  int nkc;            // C / 32
+  float sumelems;
+};
+
+// ---------------------------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok;
+}
+// Bounded wait: a protocol bug traps (launch fails with an error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000LL) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, kind::tf32 (fp32 bit patterns, low 13 mantissa bits ignored), fp32 accumulate
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32 consecutive columns: thread i of the warp gets TMEM lane (base_lane + i), columns col .. col+31
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: rows of 128 B, 8-row atoms 1024 B apart.
+// (bit layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor -- start[0,14) LBO[16,30) SBO[32,46) version[46,48)
+//  layout_type[61,64), all byte quantities >> 4.)
+__device__ __forceinline__ uint64_t desc_sw128_kmajor(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;             // LBO: unused for swizzled K-major
+  d |= (uint64_t)(1024 >> 4) << 32;   // SBO
+  d |= (uint64_t)1 << 46;             // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;             // SWIZZLE_128B
+  return d;
+}
+// Instruction descriptor (InstrDescriptor): c=F32 [4,6), a=TF32 [7,10), b=TF32 [10,13), K-major both, N>>3 [17,23),
+// M>>4 [24,29)
+__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+struct __align__(8) Barriers {
+  uint64_t a_full;
+  uint64_t full[NSTAGE];
+  uint64_t empty[NSTAGE];
+  uint64_t tmem_full[NBUF];
+  uint64_t tmem_empty[NBUF];
+  uint32_t tmem_base;
+};
+
+constexpr int STG_STRIDE_MAX = 34;  // floats per staged pixel row (>= gw, even => conflict-free writes)
+
+// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 16 KB][stage: 4 warps x 32 x STG floats][barriers]
+template <int R>
+__global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_constant__ TcParams P) {
+  constexpr int GW = 2 * R + 1;
+  constexpr int SS = (GW + 1) & ~1;  // even stride >= GW: lane stride (SS-1) is odd => bank-conflict-free
+  static_assert(SS <= STG_STRIDE_MAX, "window too wide");
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)P.nkc * CHUNK_BYTES;
+  float* sStage = reinterpret_cast<float*>(sB + (size_t)NSTAGE * CHUNK_BYTES);
+  Barriers* bars = reinterpret_cast<Barriers*>(sStage + 4 * 32 * STG_STRIDE_MAX);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- which tile ----
+  int t = blockIdx.x;
+  const int tx = t % P.TX; t /= P.TX;
+  const int ty = t % P.TY; t /= P.TY;
+  const int cls = t % P.ncls;
+  const int n = t / P.ncls;
+  const int cy = cls / P.s2, cx = cls % P.s2;
+  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
+  const int y0 = ty * TILE_R, x0 = tx * TILE_C;
+  if (y0 >= Hc || x0 >= Wc) return;  // whole CTA leaves together, before any barrier exists
+  const int s_first = max(0, y0 - R);
+  const int s_last = min(Hc - 1, y0 + TILE_R - 1 + R);
+  const int nblk = (s_last - s_first + 1 + 3) / 4;   // blocks of 4 b-rows (32 px each)
+  const int nkc = P.nkc;
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bars->a_full), 1);
+    for (int i = 0; i < NSTAGE; ++i) { mbar_init(smem_u32(&bars->full[i]), 1); mbar_init(smem_u32(&bars->empty[i]), 1); }
+    for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      const uint32_t a_full = smem_u32(&bars->a_full);
+      mbar_expect_tx(a_full, (uint32_t)nkc * CHUNK_BYTES);
+      for (int kc = 0; kc < nkc; ++kc)
+        tma_load_4d(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls], a_full, kc * KCH, x0, y0, n);
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int srow = s_first + blk * 4;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % NSTAGE;
+          mbar_wait(smem_u32(&bars->empty[stage]), ((it / NSTAGE) & 1) ^ 1);
+          const uint32_t full = smem_u32(&bars->full[stage]);
+          mbar_expect_tx(full, CHUNK_BYTES);
+          tma_load_4d(smem_u32(sB + (size_t)stage * CHUNK_BYTES), &P.b[cls], full, kc * KCH, x0, srow, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      constexpr uint32_t idesc = idesc_tf32(128, BLK_N);
+      mbar_wait(smem_u32(&bars->a_full), 0);
+      tc_fence_after();
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int buf = blk % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((blk / NBUF) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)buf * BLK_N;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % NSTAGE;
+          mbar_wait(smem_u32(&bars->full[stage]), (it / NSTAGE) & 1);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + (size_t)kc * CHUNK_BYTES);
+          const uint32_t b_addr = smem_u32(sB + (size_t)stage * CHUNK_BYTES);
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)  // K = 8 tf32 = 32 bytes per instruction inside the 128-byte swizzle row
+            umma_tf32(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
+                      (uint32_t)((kc | k4) != 0));
+          umma_commit(smem_u32(&bars->empty[stage]));   // frees the B stage when these MMAs have read it
+        }
+        umma_commit(smem_u32(&bars->tmem_full[buf]));   // accumulator block complete
+      }
+    }
+  } else {
+    // ================================ epilogue (warps 2..5) ================================
+    const int q = warp & 3;              // TMEM lane quadrant this warp may read = a-row of the tile
+    const int y = y0 + q;                // class-space row of this warp's 32 pixels
+    const int c = lane;                  // class-space column offset
+    float* stg = sStage + q * 32 * STG_STRIDE_MAX;
+    const bool row_ok = y < Hc;
+    const int Y = y * P.s2 + cy;         // full-resolution row
+    const size_t rowbase = ((size_t)n * P.H + (row_ok ? Y : 0)) * P.W;
+    const int ncol = min(TILE_C, Wc - x0);
+
+    // displacement rows that point outside the image: written as zeros here, never computed
+    if (row_ok) {
+      const int dlo = max(0, R - y) * GW;                 // p < -y
+      const int dhi = min(GW, Hc - y + R) * GW;           // p > Hc-1-y
+      for (int cc = 0; cc < ncol; ++cc) {
+        float* po = P.out + (rowbase + (size_t)((x0 + cc) * P.s2 + cx)) * P.D;
+        for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
+        for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
+      }
+    }
+
+    for (int blk = 0; blk < nblk; ++blk) {
+      const int buf = blk % NBUF;
+      mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int br = 0; br < 4; ++br) {
+        const int s = s_first + blk * 4 + br;
+        const int p = s - y;
+        if (!(row_ok && p >= -R && p <= R && s < Hc)) continue;   // warp-uniform
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
+        // scatter my row's window into the staging row: stg[c][o + R] = S[c][xb = c + o], zero outside the image
+#pragma unroll
+        for (int jj = 0; jj < 32 + 2 * R; ++jj) {
+          const int j = jj - R;               // b column
+          const int idx = jj - c;             // = (j - c) + R
+          if (idx >= 0 && idx < GW) stg[c * SS + idx] = (j >= 0 && j < 32) ? v[(j >= 0 && j < 32) ? j : 0] : 0.f;
+        }
+        __syncwarp();
+        const int dbase = (p + R) * GW;
+#pragma unroll 1
+        for (int tt = 0; tt < GW; ++tt) {
+          const int e = tt * 32 + lane;
+          const int cc = e / GW, o = e - cc * GW;
+          if (cc < ncol) {
+            float* po = P.out + (rowbase + (size_t)((x0 + cc) * P.s2 + cx)) * P.D + dbase + o;
+            *po = __fdiv_rn(stg[cc * SS + o], P.sumelems);
+          }
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// Tensor map over one parity class of an NHWC fp32 tensor: dims (C, Wc, Hc, N), box (32, box_w, box_h, 1), SW128.
+bool make_class_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int s2, int cy, int cx, int Hc,
+                    int Wc, int box_w, int box_h) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Wc, (cuuint64_t)Hc, (cuuint64_t)N};
+  const cuuint64_t strides[3] = {(cuuint64_t)s2 * C * 4, (cuuint64_t)s2 * W * C * 4, (cuuint64_t)H * W * C * 4};
+  const cuuint32_t box[4] = {KCH, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  void* addr = const_cast<float*>(base + ((size_t)cy * W + cx) * C);
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, addr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+size_t fwd_smem_bytes(int nkc) {
+  return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)NSTAGE * CHUNK_BYTES + 4 * 32 * STG_STRIDE_MAX * sizeof(float) +
+         sizeof(Barriers);
+}
+
+}  // namespace
+
+bool corr_tc_supported(const CorrGeom& g, int precision) {
+  if (precision != FN2_PREC_TF32) return false;
+  if (g.k != 1 || g.s1 != 1 || g.pad != g.md) return false;
+  if (g.s2 != 1 && g.s2 != 2) return false;
+  if (g.r != 10) return false;                       // window radius instantiated below
+  if (g.C % KCH != 0 || g.C / KCH > MAX_KC) return false;
+  const int Wc0 = (g.W + g.s2 - 1) / g.s2;
+  if (Wc0 > TILE_C) return false;                    // single column tile for now (cfg1/cfg3 shapes)
+  return true;
+}
+
 size_t corr_tc_workspace_bytes(const CorrGeom&, int, int) { return 0; }
-int corr_tc_forward(const CorrGeom&, const float*, const float*, float*, int, void*, size_t, cudaStream_t) { return FN2_E_UNSUPPORTED_PRECISION; }
-int corr_tc_backward(const CorrGeom&, const float*, const float*, const float*, float*, float*, int, void*, size_t, cudaStream_t) { return FN2_E_UNSUPPORTED_PRECISION; }
+
+int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void*, size_t,
+                    cudaStream_t st) {
+  if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  TcParams P;
+  P.out = out;
+  P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
+  for (int c = 0; c < 2; ++c) {
+    P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
+    P.Wc[c] = c < g.s2 ? (g.W - c + g.s2 - 1) / g.s2 : 0;
+  }
+  P.TY = (P.Hc[0] + TILE_R - 1) / TILE_R;
+  P.TX = (P.Wc[0] + TILE_C - 1) / TILE_C;
+  P.nkc = g.C / KCH;
+  P.sumelems = (float)g.C;
+  for (int cls = 0; cls < P.ncls; ++cls) {
+    const int cy = cls / g.s2, cx = cls % g.s2;
+    if (P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // empty class (H or W == 1 with s2 == 2): map class 0 instead, never used
+      P.a[cls] = P.a[0]; P.b[cls] = P.b[0];
+      continue;
+    }
+    if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, TILE_R) ||
+        !make_class_map(&P.b[cls], b, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, 4))
+      return FN2_E_CUDA;
+  }
+  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }
+  const size_t smem = fwd_smem_bytes(P.nkc);
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)fwd_smem_bytes(MAX_KC));
+  });
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
+  const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
+  if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  corr_tc_fwd_kernel<10><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  return after_launch();
+}
+
+int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
+                     int precision, void*, size_t, cudaStream_t st) {
+  // the tensor-core backward is not written yet: fp32 CUDA-core path keeps the op differentiable in every mode
+  if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  if (corr_simt_supported(g)) return corr_simt_backward(g, gout, a, b, ga, gb, st);
+  return corr_generic_backward(g, gout, a, b, ga, gb, st);
+}
+
 }  // namespace fn2

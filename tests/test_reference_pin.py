@@ -12,11 +12,15 @@ from conftest import assert_close, corr_inputs, grad_like, warp_inputs
 
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built")]
 
+# Shapes are chosen with H*W % 16 == 0 (or pad >= 16): otherwise the reference's PadData takes its early-return
+# branch (pad.cu.cc:31-33) and writes zeros at un-padded coordinates of the padded tensor, racing with / clobbering
+# real data when pad < 16 -- a defect of the reference that is deliberately not reproduced.
 CASES = [
-    (2, 9, 11, 8, 1, 4, 1, 2, 4),
-    (1, 10, 12, 5, 3, 3, 2, 2, 3),
-    (1, 12, 10, 6, 3, 2, 1, 1, 4),
+    (2, 8, 12, 8, 1, 4, 1, 2, 4),
+    (1, 8, 12, 5, 3, 3, 2, 2, 3),
+    (1, 12, 12, 6, 3, 2, 1, 1, 4),
     (1, 16, 16, 32, 1, 4, 1, 1, 4),
+    (1, 14, 18, 32, 1, 20, 1, 2, 20),
     (1, 24, 32, 256, 1, 20, 1, 2, 20),
     (1, 48, 64, 256, 1, 20, 1, 2, 20),
 ]
