@@ -12,7 +12,8 @@
 // the +-r window out of each TMEM row, restage it through shared memory and write the 441-channel output coalesced.
 // Zero padding is TMA out-of-bounds fill; b-rows outside the image are never loaded, their outputs are written as 0.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = epilogue.
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = epilogue
+// (two warps per TMEM lane quadrant, taking alternate b-rows).
 #include <cuda.h>
 #include <mutex>
 #include "fn2_common.cuh"
@@ -25,10 +26,12 @@ constexpr int TILE_C = 32;         // a-cols per tile
 constexpr int KCH = 32;            // channels per K-chunk = one 128-byte swizzle row
 constexpr int BLK_N = 128;         // b-pixels per accumulator block
 constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 128 B
-constexpr int NSTAGE = 5;          // B ring depth
+constexpr int NSTAGE = 4;          // B ring depth
 constexpr int NBUF = 4;            // TMEM accumulator buffers (4 x 128 columns = 512)
 constexpr int MAX_KC = 8;          // C <= 256
-constexpr int NTHREADS = 192;
+constexpr int NEPI = 8;            // epilogue warps: two per TMEM lane quadrant
+constexpr int NTHREADS = 64 + 32 * NEPI;
+constexpr int STG_FLOATS = 32 * 33;  // per-warp transposed staging tile [b column][a column], pitch 33
 
 struct TcParams {
   CUtensorMap a[4];
@@ -146,20 +149,18 @@ struct __align__(8) Barriers {
   uint32_t tmem_base;
 };
 
-constexpr int STG_STRIDE_MAX = 34;  // floats per staged pixel row (>= gw, even => conflict-free writes)
 
-// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 16 KB][stage: 4 warps x 32 x STG floats][barriers]
+// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 16 KB][staging: NEPI x 32x33 floats][barriers]
 template <int R>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_constant__ TcParams P) {
   constexpr int GW = 2 * R + 1;
-  constexpr int SS = (GW + 1) & ~1;  // even stride >= GW: lane stride (SS-1) is odd => bank-conflict-free
-  static_assert(SS <= STG_STRIDE_MAX, "window too wide");
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // keep shared-space provenance (plain LDS/STS, not generic LD/ST): index the array instead of casting through ints
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = sA + (size_t)P.nkc * CHUNK_BYTES;
   float* sStage = reinterpret_cast<float*>(sB + (size_t)NSTAGE * CHUNK_BYTES);
-  Barriers* bars = reinterpret_cast<Barriers*>(sStage + 4 * 32 * STG_STRIDE_MAX);
+  Barriers* bars = reinterpret_cast<Barriers*>(sStage + NEPI * STG_FLOATS);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -181,7 +182,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars->a_full), 1);
     for (int i = 0; i < NSTAGE; ++i) { mbar_init(smem_u32(&bars->full[i]), 1); mbar_init(smem_u32(&bars->empty[i]), 1); }
-    for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), 4); }
+    for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), NEPI); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -238,22 +239,42 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
       }
     }
   } else {
-    // ================================ epilogue (warps 2..5) ================================
+    // ================================ epilogue (warps 2..9) ================================
+    const int ew = warp - 2;
     const int q = warp & 3;              // TMEM lane quadrant this warp may read = a-row of the tile
+    const int half = ew >> 2;            // the two warps of a quadrant take alternate b-rows
     const int y = y0 + q;                // class-space row of this warp's 32 pixels
-    const int c = lane;                  // class-space column offset
-    float* stg = sStage + q * 32 * STG_STRIDE_MAX;
+    float* stg = sStage + ew * STG_FLOATS;
     const bool row_ok = y < Hc;
     const int Y = y * P.s2 + cy;         // full-resolution row
-    const size_t rowbase = ((size_t)n * P.H + (row_ok ? Y : 0)) * P.W;
     const int ncol = min(TILE_C, Wc - x0);
+    const float inv = 1.0f / P.sumelems;
+    // first output element of this warp's pixel row (pixel column x0 of the class)
+    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.D;
+    const int pixstride = P.s2 * P.D;    // floats between neighbouring pixels of the class
+
+    // Per-lane plan for writing one displacement row (32 pixels x GW values, 84-byte runs) coalesced:
+    // element e = tt*32 + lane -> pixel cc = e / GW, displacement o = e % GW, source column xb = cc + o - R.
+    int rd[GW], gl[GW];
+    uint32_t xmask = 0, smask = 0;
+#pragma unroll
+    for (int tt = 0; tt < GW; ++tt) {
+      const int e = tt * 32 + lane;
+      const int cc = e / GW, o = e - cc * GW;
+      const int xb = cc + o - R;
+      const bool xok = (xb >= 0) && (xb < 32);
+      rd[tt] = xok ? xb * 33 + cc : 0;
+      gl[tt] = cc * pixstride + o;
+      xmask |= (xok ? 1u : 0u) << tt;
+      smask |= ((cc < ncol) ? 1u : 0u) << tt;
+    }
 
     // displacement rows that point outside the image: written as zeros here, never computed
     if (row_ok) {
       const int dlo = max(0, R - y) * GW;                 // p < -y
       const int dhi = min(GW, Hc - y + R) * GW;           // p > Hc-1-y
-      for (int cc = 0; cc < ncol; ++cc) {
-        float* po = P.out + (rowbase + (size_t)((x0 + cc) * P.s2 + cx)) * P.D;
+      for (int cc = half; cc < ncol; cc += 2) {
+        float* po = orow0 + (size_t)cc * pixstride;
         for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
         for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
       }
@@ -263,32 +284,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
       const int buf = blk % NBUF;
       mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int br = 0; br < 4; ++br) {
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const int br = half + 2 * h2;
         const int s = s_first + blk * 4 + br;
         const int p = s - y;
-        if (!(row_ok && p >= -R && p <= R && s < Hc)) continue;   // warp-uniform
-        float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
-        // scatter my row's window into the staging row: stg[c][o + R] = S[c][xb = c + o], zero outside the image
+        if (row_ok && p >= -R && p <= R && s < Hc) {   // warp-uniform
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
 #pragma unroll
-        for (int jj = 0; jj < 32 + 2 * R; ++jj) {
-          const int j = jj - R;               // b column
-          const int idx = jj - c;             // = (j - c) + R
-          if (idx >= 0 && idx < GW) stg[c * SS + idx] = (j >= 0 && j < 32) ? v[(j >= 0 && j < 32) ? j : 0] : 0.f;
-        }
-        __syncwarp();
-        const int dbase = (p + R) * GW;
-#pragma unroll 1
-        for (int tt = 0; tt < GW; ++tt) {
-          const int e = tt * 32 + lane;
-          const int cc = e / GW, o = e - cc * GW;
-          if (cc < ncol) {
-            float* po = P.out + (rowbase + (size_t)((x0 + cc) * P.s2 + cx)) * P.D + dbase + o;
-            *po = __fdiv_rn(stg[cc * SS + o], P.sumelems);
+          for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+          __syncwarp();
+          float* orow = orow0 + (p + R) * GW;
+#pragma unroll
+          for (int tt = 0; tt < GW; ++tt) {
+            float x = stg[rd[tt]];
+            x = ((xmask >> tt) & 1u) ? x * inv : 0.f;
+            if ((smask >> tt) & 1u) orow[gl[tt]] = x;
           }
+          __syncwarp();
         }
-        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
@@ -338,7 +353,7 @@ bool make_class_map(CUtensorMap* m, const float* base, int N, int H, int W, int 
 }
 
 size_t fwd_smem_bytes(int nkc) {
-  return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)NSTAGE * CHUNK_BYTES + 4 * 32 * STG_STRIDE_MAX * sizeof(float) +
+  return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)NSTAGE * CHUNK_BYTES + (size_t)NEPI * STG_FLOATS * sizeof(float) +
          sizeof(Barriers);
 }
 
