@@ -14,16 +14,15 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = epilogue
 // (two warps per TMEM lane quadrant, taking alternate b-rows).
-#include <cuda.h>
-#include <mutex>
-#include "fn2_common.cuh"
+#include "fn2_tc.cuh"
 
 namespace fn2 {
 namespace {
 
+using namespace tc;
+
 constexpr int TILE_R = 4;          // a-rows per tile (class space)
 constexpr int TILE_C = 32;         // a-cols per tile
-constexpr int KCH = 32;            // channels per K-chunk = one 128-byte swizzle row
 constexpr int BLK_N = 128;         // b-pixels per accumulator block
 constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 128 B
 constexpr int NSTAGE = 4;          // B ring depth
@@ -43,102 +42,6 @@ struct TcParams {
   int nkc;            // C / 32
   float sumelems;
 };
-
-// ---------------------------------------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok;
-}
-// Bounded wait: a protocol bug traps (launch fails with an error) instead of hanging the GPU.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
-  }
-}
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
-                                            int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, kind::tf32 (fp32 bit patterns, low 13 mantissa bits ignored), fp32 accumulate
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// 32 lanes x 32 consecutive columns: thread i of the warp gets TMEM lane (base_lane + i), columns col .. col+31
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-  uint32_t r[32];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// UMMA shared-memory descriptor, K-major, SWIZZLE_128B: rows of 128 B, 8-row atoms 1024 B apart.
-// (bit layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor -- start[0,14) LBO[16,30) SBO[32,46) version[46,48)
-//  layout_type[61,64), all byte quantities >> 4.)
-__device__ __forceinline__ uint64_t desc_sw128_kmajor(uint32_t saddr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)1 << 16;             // LBO: unused for swizzled K-major
-  d |= (uint64_t)(1024 >> 4) << 32;   // SBO
-  d |= (uint64_t)1 << 46;             // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;             // SWIZZLE_128B
-  return d;
-}
-// Instruction descriptor (InstrDescriptor): c=F32 [4,6), a=TF32 [7,10), b=TF32 [10,13), K-major both, N>>3 [17,23),
-// M>>4 [24,29)
-__host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
-  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
 
 struct __align__(8) Barriers {
   uint64_t a_full;
@@ -319,39 +222,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
   }
 }
 
-// ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
-// Tensor map over one parity class of an NHWC fp32 tensor: dims (C, Wc, Hc, N), box (32, box_w, box_h, 1), SW128.
-bool make_class_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int s2, int cy, int cx, int Hc,
-                    int Wc, int box_w, int box_h) {
-  EncodeTiledFn enc = get_encode();
-  if (!enc) return false;
-  const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Wc, (cuuint64_t)Hc, (cuuint64_t)N};
-  const cuuint64_t strides[3] = {(cuuint64_t)s2 * C * 4, (cuuint64_t)s2 * W * C * 4, (cuuint64_t)H * W * C * 4};
-  const cuuint32_t box[4] = {KCH, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
-  const cuuint32_t estr[4] = {1, 1, 1, 1};
-  void* addr = const_cast<float*>(base + ((size_t)cy * W + cx) * C);
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, addr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
-}
-
 size_t fwd_smem_bytes(int nkc) {
   return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)NSTAGE * CHUNK_BYTES + (size_t)NEPI * STG_FLOATS * sizeof(float) +
          sizeof(Barriers);
@@ -413,8 +283,9 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
 
 int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
                      int precision, void*, size_t, cudaStream_t st) {
-  // the tensor-core backward is not written yet: fp32 CUDA-core path keeps the op differentiable in every mode
   if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  if (corr_tc_bwd_supported(g, precision)) return corr_tc_backward_launch(g, gout, a, b, ga, gb, precision, st);
+  // shapes the tensor-core backward does not cover: the fp32 CUDA-core path keeps the op differentiable
   if (corr_simt_supported(g)) return corr_simt_backward(g, gout, a, b, ga, gb, st);
   return corr_generic_backward(g, gout, a, b, ga, gb, st);
 }

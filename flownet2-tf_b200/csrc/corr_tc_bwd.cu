@@ -1,0 +1,282 @@
+// corr_tc_bwd.cu -- FlowNetC correlation BACKWARD on the 5th-generation tensor cores (tcgen05 + TMEM + TMA), sm_100a.
+//
+// Formulation (kernel_size 1, stride_1 1, pad == max_displacement; flownet_c.py:40, correlation_grad_kernel.cu.cc):
+//   da[i,c] = 1/C * sum_j G[i,j] * b[j,c]          db[j,c] = 1/C * sum_i G[i,j] * a[i,c]
+// where, inside one (y%s2, x%s2) parity class, i = (ya,xa) and j = (yb,xb) are pixels of the half-resolution grid and
+//   G[i,j] = grad[n, i, (yb-ya+r)*gw + (xb-xa+r)]  if |yb-ya| <= r and |xb-xa| <= r, else 0
+// is the banded "gradient Gram matrix".  Both gradients are dense GEMMs against G, so no scatter and no atomics:
+// every output element is produced by exactly one CTA.
+//
+// One CTA owns a tile of 4 class-rows x 32 class-cols of OUTPUT pixels (a-pixels for da: mode 0, b-pixels for db:
+// mode 1) and all C channels, and walks over the <= 4+2r source rows t of the other tensor X (b for da, a for db):
+//   D^T[c, out pixel] += X_t^T[c, src pixel] * Gblk_t[src pixel, out pixel]       (M = 128 channels, N = 128, K = 32)
+//   * X_t (32 pixels x C channels, NHWC) arrives by TMA as C/32 chunks of [32 pixels][32 channels] (swizzle
+//     128B_ATOM_32B, the one layout the tensor core accepts for an MN-major 32-bit operand); read as the MN-major A
+//     operand (channels contiguous) -- no transpose, no conversion: fp32 bits are consumed as tf32.
+//   * Gblk_t is built by eight warps straight from `gradients` into shared memory in the same swizzled layout: four
+//     32x32 blocks (one per output row of the tile), rows = a-pixel, cols = b-pixel, each row the 21-float run
+//     grad[i, p, :] shifted to its diagonal position.  The same bytes are a K-major B operand for da (N = a-pixel
+//     rows, K = b-pixel cols) and an MN-major B operand for db (N = b-pixel cols, K = a-pixel rows).
+//   * the accumulator D^T (2 halves of 128 channels x 128 output pixels, fp32) lives in 256 TMEM columns; after the
+//     last source row the same eight warps read it back (lane = channel) and store 128-byte channel runs.
+// CTAs of the two modes for the same image are adjacent in the grid so the second read of `gradients` hits L2.
+//
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = G builders, then
+// epilogue.
+#include "fn2_tc.cuh"
+
+namespace fn2 {
+namespace {
+
+using namespace tc;
+
+constexpr int TILE_R = 4;                 // output rows per tile (class space)
+constexpr int TILE_C = 32;                // output cols per tile
+constexpr int XCHUNK = 32 * 128;          // one X chunk: 32 pixels x 32 channels fp32 = 4 KB
+constexpr int MAX_CH = 8;                 // C <= 256
+constexpr int XSTAGE = MAX_CH * XCHUNK;   // 32 KB per stage
+constexpr int GBLOCK = 32 * 128;          // one G block: 32 a-pixels x 32 b-pixels fp32 = 4 KB
+constexpr int GSTAGE = TILE_R * GBLOCK;   // 16 KB per stage
+constexpr int NBUILD = 8;                 // builder / epilogue warps
+constexpr int NTHREADS = 64 + 32 * NBUILD;
+constexpr int TMEM_COLS = 256;
+
+struct BwdParams {
+  CUtensorMap x[2][4];  // [mode][class]: mode 0 (da) streams b, mode 1 (db) streams a
+  const float* grad;
+  float* out[2];        // da, db
+  int N, H, W, C, D, s2, ncls, R, GW;
+  int Hc[2], Wc[2];
+  int TY;
+  int nchunk;           // C / 32
+  int nhalf;            // ceil(C / 128)
+  float inv;            // 1 / C
+};
+
+template <int NST>
+struct __align__(8) BwdBarriers {
+  uint64_t x_full[NST];
+  uint64_t g_full[NST];
+  uint64_t empty[NST];
+  uint64_t acc_full;
+  uint32_t tmem_base;
+};
+
+template <int NST>
+constexpr size_t bwd_smem_bytes() {
+  return 1024 + (size_t)NST * (XSTAGE + GSTAGE) + sizeof(BwdBarriers<NST>);
+}
+
+template <int NST, int MINB>
+__global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sX = smem;
+  uint8_t* sG = sX + (size_t)NST * XSTAGE;
+  BwdBarriers<NST>* bars = reinterpret_cast<BwdBarriers<NST>*>(sG + (size_t)NST * GSTAGE);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- which tile: ((n * ncls + cls) * TY + ty) * 2 + mode ----
+  int t = blockIdx.x;
+  const int mode = t & 1; t >>= 1;
+  const int ty = t % P.TY; t /= P.TY;
+  const int cls = t % P.ncls;
+  const int n = t / P.ncls;
+  const int cy = cls / P.s2, cx = cls % P.s2;
+  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
+  const int r0 = ty * TILE_R;
+  if (r0 >= Hc || Wc < 1) return;  // whole CTA leaves together, before any barrier exists
+  const int R = P.R;
+  const int t_first = max(0, r0 - R);
+  const int t_last = min(Hc - 1, r0 + TILE_R - 1 + R);
+  const int nrows = t_last - t_first + 1;
+  const int nchunk = P.nchunk;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NST; ++i) {
+      mbar_init(smem_u32(&bars->x_full[i]), 1);
+      mbar_init(smem_u32(&bars->g_full[i]), NBUILD);
+      mbar_init(smem_u32(&bars->empty[i]), 1);
+    }
+    mbar_init(smem_u32(&bars->acc_full), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================ TMA producer: one source row of X per stage ================================
+    if (lane == 0) {
+      const CUtensorMap* map = &P.x[mode][cls];
+      for (int it = 0; it < nrows; ++it) {
+        const int stage = it % NST;
+        mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
+        const uint32_t full = smem_u32(&bars->x_full[stage]);
+        mbar_expect_tx(full, (uint32_t)nchunk * XCHUNK);
+        for (int c = 0; c < nchunk; ++c)
+          tma_load_4d(smem_u32(sX + (size_t)stage * XSTAGE + (size_t)c * XCHUNK), map, full, c * KCH, 0, t_first + it, n);
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      // A = X^T: MN-major (channels contiguous), M = 128 channels = 4 chunks (LBO = chunk stride), K = 8 pixel rows.
+      // B = G  : mode 0 K-major (N = a-pixel rows, K = b-pixel cols); mode 1 MN-major (N = b-pixel cols, LBO = block
+      //          stride, K = a-pixel rows).
+      const uint32_t idesc = idesc_tf32_major(128, 128, 1, mode);
+      for (int it = 0; it < nrows; ++it) {
+        const int stage = it % NST;
+        const uint32_t par = (it / NST) & 1;
+        mbar_wait(smem_u32(&bars->x_full[stage]), par);
+        mbar_wait(smem_u32(&bars->g_full[stage]), par);
+        tc_fence_after();
+        const uint32_t x_addr = smem_u32(sX + (size_t)stage * XSTAGE);
+        const uint32_t g_addr = smem_u32(sG + (size_t)stage * GSTAGE);
+        for (int h = 0; h < P.nhalf; ++h) {
+#pragma unroll
+          for (int k8 = 0; k8 < 4; ++k8) {
+            const uint64_t adesc = desc_sw128b32_mnmajor(x_addr + h * 4 * XCHUNK + k8 * 1024, XCHUNK, 512);
+            const uint64_t bdesc = mode ? desc_sw128b32_mnmajor(g_addr + k8 * 1024, GBLOCK, 512)
+                                        : desc_sw128_kmajor(g_addr + k8 * 32);
+            umma_tf32(tmem_base + (uint32_t)h * 128, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
+          }
+        }
+        umma_commit(smem_u32(&bars->empty[stage]));  // frees X and G of this stage once the MMAs have read them
+      }
+      umma_commit(smem_u32(&bars->acc_full));
+    }
+  } else {
+    // ================================ G builders (warps 2..9), then epilogue ================================
+    const int bw = warp - 2;
+    const int q = bw >> 1;            // block = output row r0 + q of the tile
+    const int xh = (bw & 1) * 16;     // this warp fills a-pixel rows xh .. xh+15 of the block
+    const int GW = P.GW;
+    const int xb = lane;              // column of the block = b-pixel
+    for (int it = 0; it < nrows; ++it) {
+      const int stage = it % NST;
+      const int tt = t_first + it;
+      // a-row and displacement row of this block for this source row
+      const int ya = mode ? tt : r0 + q;
+      const int p = mode ? (r0 + q - tt) : (tt - (r0 + q));
+      const bool blk_ok = (ya < Hc) && (r0 + q < Hc) && (p >= -R) && (p <= R);
+      float v[16];
+      const float* grow = P.grad + (((size_t)n * P.H + (size_t)(ya * P.s2 + cy)) * P.W + cx) * P.D + (p + R) * GW;
+#pragma unroll
+      for (int rr = 0; rr < 16; ++rr) {
+        const int x = xh + rr;
+        const int o = xb - x + R;
+        const bool ok = blk_ok && (x < Wc) && (xb < Wc) && (o >= 0) && (o < GW);
+        v[rr] = ok ? __ldg(grow + (size_t)x * P.s2 * P.D + o) : 0.f;
+      }
+      mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
+      uint8_t* blk = sG + (size_t)stage * GSTAGE + (size_t)q * GBLOCK;
+#pragma unroll
+      for (int rr = 0; rr < 16; ++rr) {
+        const int x = xh + rr;
+        // mode 0: K-major operand, SWIZZLE_128B (16-byte chunk ^ (row & 7)); mode 1: MN-major operand,
+        // SWIZZLE_128B_BASE32B (32-byte unit ^ (row & 3))
+        const int off = mode ? ((((xb >> 3) ^ (x & 3)) << 5) | ((xb & 7) << 2))
+                             : ((((xb >> 2) ^ (x & 7)) << 4) | ((xb & 3) << 2));
+        *reinterpret_cast<float*>(blk + x * 128 + off) = v[rr];
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars->g_full[stage]));
+    }
+
+    // ---- epilogue: D^T[channel lane, output pixel column] -> out[pixel, channel] ----
+    mbar_wait(smem_u32(&bars->acc_full), 0);
+    tc_fence_after();
+    const int qd = warp & 3;        // TMEM lane quadrant this warp may read
+    const int e = bw >> 2;          // the two warps of a quadrant take alternate output rows
+    float* outp = P.out[mode];
+    const int ncol = min(TILE_C, Wc);
+    const float inv = P.inv;
+    for (int h = 0; h < P.nhalf; ++h) {
+      const int ch = h * 128 + qd * 32 + lane;
+      for (int qq = e; qq < TILE_R; qq += 2) {
+        const int row = r0 + qq;
+        if (row >= Hc) continue;    // warp-uniform
+        float v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * 128 + qq * 32), v);
+        float* orow = outp + (((size_t)n * P.H + (size_t)(row * P.s2 + cy)) * P.W + cx) * P.C + ch;
+        if (ch < P.C) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < ncol) orow[(size_t)j * P.s2 * P.C] = v[j] * inv;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+constexpr int BWD_NST = 4;
+
+}  // namespace
+
+bool corr_tc_bwd_supported(const CorrGeom& g, int precision) {
+  if (precision != FN2_PREC_TF32) return false;
+  if (g.k != 1 || g.s1 != 1 || g.pad != g.md) return false;
+  if (g.s2 != 1 && g.s2 != 2) return false;
+  if (g.C % KCH != 0 || g.C / KCH > MAX_CH) return false;
+  const int Wc0 = (g.W + g.s2 - 1) / g.s2;
+  if (Wc0 > TILE_C) return false;  // single column tile for now (cfg1/cfg3 shapes)
+  return true;
+}
+
+int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
+                            int precision, cudaStream_t st) {
+  if (!corr_tc_bwd_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  BwdParams P;
+  P.grad = gout;
+  P.out[0] = ga; P.out[1] = gb;
+  P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
+  P.R = g.r; P.GW = g.gw;
+  for (int c = 0; c < 2; ++c) {
+    P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
+    P.Wc[c] = c < g.s2 ? (g.W - c + g.s2 - 1) / g.s2 : 0;
+  }
+  P.TY = (P.Hc[0] + TILE_R - 1) / TILE_R;
+  P.nchunk = g.C / KCH;
+  P.nhalf = (g.C + 127) / 128;
+  P.inv = 1.0f / (float)g.C;
+  for (int mode = 0; mode < 2; ++mode) {
+    const float* src = mode ? a : b;
+    for (int cls = 0; cls < 4; ++cls) {
+      const int cy = cls / g.s2, cx = cls % g.s2;
+      if (cls >= P.ncls || P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // unused / empty class: any valid map, never dereferenced
+        P.x[mode][cls] = P.x[mode][0];
+        continue;
+      }
+      if (!make_class_map(&P.x[mode][cls], src, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, 1,
+                          CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
+        return FN2_E_CUDA;
+    }
+  }
+  auto kern = corr_tc_bwd_kernel<BWD_NST, 1>;
+  constexpr size_t smem = bwd_smem_bytes<BWD_NST>();
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  });
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
+  const long long grid = (long long)g.N * P.ncls * P.TY * 2;
+  if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  kern<<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  return after_launch();
+}
+
+}  // namespace fn2

@@ -41,6 +41,10 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
                     size_t ws_bytes, cudaStream_t st);
 int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
                      int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+// corr_tc_bwd.cu
+bool corr_tc_bwd_supported(const CorrGeom& g, int precision);
+int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
+                            int precision, cudaStream_t st);
 
 int flow_warp_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
                       cudaStream_t st);
