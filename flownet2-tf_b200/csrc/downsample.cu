@@ -9,10 +9,23 @@
 // shares one output pixel: the taps are dealt to the group row by row so that consecutive lanes read consecutive
 // input pixels (coalesced, all C channels of a pixel by one lane), and the three sums are reduced with shuffles.
 // HBM-bound: every input byte is read once from DRAM (re-reads of overlapping windows hit L2).
+//
+// Fast path (C <= 4, in_w <= 1024): downsample_strip_kernel.  The weight is separable, w = wx(x) * wy(y), and a tap
+// with w == 0 adds exact zeros to all three sums, so only the <= 2 (3 with rounding slack) output columns whose
+// triangle covers an input column matter.  One CTA owns one output row (n, dy): thread x walks input column x down
+// the rows of the window with fully coalesced row reads (in_w * C floats per row), keeping value/weight/NaN sums
+// for its three candidate output columns in registers; a deterministic shared-memory pass then sums the columns of
+// each output pixel.  Coarse scales (windows up to 155 rows) split the rows over a thread-block cluster of up to 8
+// CTAs and combine the partial sums through distributed shared memory, so every scale launches >= ~1500 CTAs at
+// batch 32 and each input row is read twice (from L2), not (2*hr+1)*(2*wr+1)/(hs*ws) times with 2 divisions per tap.
+#include <cooperative_groups.h>
+#include <mutex>
 #include "fn2_common.cuh"
 
 namespace fn2 {
 namespace {
+
+namespace cg = cooperative_groups;
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MAXC = 4;
@@ -130,6 +143,175 @@ __global__ void __launch_bounds__(256) downsample_wide_kernel(DsParams p, const 
   }
 }
 
+
+// ---- fast path ------------------------------------------------------------------------------------------------
+// Output column nearest to input column x (same float expression wherever it is needed, so it is consistent).
+__device__ __forceinline__ int nearest_out_col(int x, float ws) { return (int)rintf((float)x / ws); }
+
+template <int CT>
+__global__ void __launch_bounds__(CT <= 2 ? 1024 : 512) downsample_strip_kernel(DsParams p, const float* __restrict__ in,
+                                                                float* __restrict__ out) {
+  constexpr int NV = 3 * CT;              // sums per slot: value, weight, nan for each channel
+  extern __shared__ float sm[];           // [3 slots * NV][blockDim.x] column sums, then [oW][NV] row-chunk partials
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rs = (int)cluster.num_blocks();
+  const int rank = (int)cluster.block_rank();
+  const int dy = blockIdx.y, n = blockIdx.z;
+  const int x = threadIdx.x, nthr = blockDim.x;
+  const float srcy = ((float)dy / (float)(p.oH - 1)) * (float)(p.iH - 1);
+  const int isy = (int)roundf(srcy);
+  const int ylo = max(isy - p.hr, 0), yhi = min(isy + p.hr, p.iH - 1);
+  const int chunk = (yhi - ylo + 1 + rs - 1) / rs;
+  const int yb = ylo + rank * chunk, ye = min(yhi, yb + chunk - 1);
+
+  // ---- per-column setup: three candidate output columns and their x-weights ----
+  float wx[3];
+  const int dxc = nearest_out_col(x, p.ws);
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const int dx = dxc - 1 + s;
+    wx[s] = 0.f;
+    if (x < p.iW && dx >= 0 && dx < p.oW) {
+      const float srcx = ((float)dx / (float)(p.oW - 1)) * (float)(p.iW - 1);
+      const int isx = (int)roundf(srcx);
+      if (x >= isx - p.wr && x <= isx + p.wr) wx[s] = fmaxf(0.0f, 1.0f - (fabsf((float)x - srcx) / p.ws));
+    }
+  }
+  float av[3][CT], aw[3][CT], an[3][CT];
+#pragma unroll
+  for (int s = 0; s < 3; ++s)
+#pragma unroll
+    for (int c = 0; c < CT; ++c) av[s][c] = aw[s][c] = an[s][c] = 0.f;
+
+  // ---- walk the rows of this CTA's chunk, 4 rows in flight ----
+  const float* col = in + ((size_t)n * p.iH * p.iW + (size_t)min(x, p.iW - 1)) * CT;
+  constexpr int U = 4;
+  for (int y0 = yb; y0 <= ye; y0 += U) {
+    float v[U][CT];
+    float wy[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int y = min(y0 + u, ye);
+      const float* ps = col + (size_t)y * p.iW * CT;
+      if constexpr (CT == 2) {
+        const float2 t = __ldg(reinterpret_cast<const float2*>(ps));
+        v[u][0] = t.x; v[u][1] = t.y;
+      } else if constexpr (CT == 4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(ps));
+        v[u][0] = t.x; v[u][1] = t.y; v[u][2] = t.z; v[u][3] = t.w;
+      } else {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) v[u][c] = __ldg(ps + c);
+      }
+      wy[u] = (y0 + u <= ye) ? fmaxf(0.0f, 1.0f - (fabsf((float)y - srcy) / p.hs)) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const bool live = (y0 + u <= ye);
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const float w = wx[s] * wy[u];
+#pragma unroll
+        for (int c = 0; c < CT; ++c) {
+          const float sv = v[u][c];
+          const bool isnan_ = (sv != sv);
+          if (live) {
+            an[s][c] += isnan_ ? w : 0.f;
+            av[s][c] = fmaf(isnan_ ? 0.f : sv, isnan_ ? 0.f : w, av[s][c]);
+            aw[s][c] += isnan_ ? 0.f : w;
+          }
+        }
+      }
+    }
+  }
+
+  // ---- column sums -> shared, then one warp per output pixel adds its columns in a fixed order ----
+#pragma unroll
+  for (int s = 0; s < 3; ++s)
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+      sm[((s * NV) + c) * nthr + x] = av[s][c];
+      sm[((s * NV) + CT + c) * nthr + x] = aw[s][c];
+      sm[((s * NV) + 2 * CT + c) * nthr + x] = an[s][c];
+    }
+  __syncthreads();
+  float* part = sm + (size_t)3 * NV * nthr;   // [oW][NV]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = nthr >> 5;
+  for (int dx = warp; dx < p.oW; dx += nwarp) {
+    // columns whose nearest output column is dx-1, dx or dx+1 (a superset, filtered below)
+    const int xlo = max(0, (int)floorf(((float)dx - 1.5f) * p.ws) - 1);
+    const int xhi = min(p.iW - 1, (int)ceilf(((float)dx + 1.5f) * p.ws) + 1);
+    float tot[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) tot[k] = 0.f;
+    for (int xx = xlo + lane; xx <= xhi; xx += 32) {
+      const int s = dx - nearest_out_col(xx, p.ws) + 1;
+      if (s >= 0 && s < 3) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) tot[k] += sm[(s * NV + k) * nthr + xx];
+      }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1)
+#pragma unroll
+      for (int k = 0; k < NV; ++k) tot[k] += __shfl_xor_sync(FULL, tot[k], off);
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) part[dx * NV + k] = tot[k];
+    }
+  }
+  cluster.sync();   // every rank's partials are in its shared memory (also a CTA barrier)
+  if (rank == 0) {
+    for (int idx = threadIdx.x; idx < p.oW * CT; idx += nthr) {
+      const int dx = idx / CT, c = idx - dx * CT;
+      float v_ = 0.f, w_ = 0.f, n_ = 0.f;
+      for (int r = 0; r < rs; ++r) {
+        const float* rp = cluster.map_shared_rank(part, r) + dx * NV;
+        v_ += rp[c]; w_ += rp[CT + c]; n_ += rp[2 * CT + c];
+      }
+      out[(((size_t)n * p.oH + dy) * p.oW + dx) * CT + c] = (n_ / w_ > 0.5f) ? nan_f() : v_ / w_;
+    }
+  }
+  cluster.sync();   // keep remote shared memory alive until rank 0 has read it
+}
+
+template <int CT>
+int launch_strip(const DsParams& p, const float* in, float* out, cudaStream_t st) {
+  const int nthr = ((p.iW + 31) / 32) * 32;
+  const int rows = 2 * p.hr + 1;
+  int rs = 1;
+  while (rs < 8 && rows / (rs * 2) >= 8) rs *= 2;   // >= 8 rows per CTA, at most 8 CTAs per cluster
+  const size_t smem = ((size_t)9 * CT * nthr + (size_t)p.oW * 3 * CT) * sizeof(float);
+  auto kern = downsample_strip_kernel<CT>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  });
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)rs, (unsigned)p.oH, (unsigned)p.N);
+  cfg.blockDim = dim3((unsigned)nthr);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)rs;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p, in, out);
+  if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  return after_launch();
+}
+
+bool strip_supported(const DsParams& p) {
+  if (p.C > MAXC || p.iW > (p.C <= 2 ? 1024 : 512) || p.oH > 65535 || p.N > 65535) return false;
+  const size_t smem = ((size_t)9 * p.C * (((p.iW + 31) / 32) * 32) + (size_t)p.oW * 3 * p.C) * sizeof(float);
+  return smem <= 200 * 1024;
+}
+
 template <int G>
 int launch_group(const DsParams& p, const float* in, float* out, cudaStream_t st) {
   const long long nopix = (long long)p.N * p.oH * p.oW;
@@ -157,6 +339,14 @@ int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C
     if (blocks > 148LL * 32) blocks = 148LL * 32;
     downsample_wide_kernel<<<(unsigned)blocks, 256, 0, st>>>(p, in, out);
     return after_launch();
+  }
+  if (strip_supported(p)) {
+    switch (C) {
+      case 1: return launch_strip<1>(p, in, out, st);
+      case 2: return launch_strip<2>(p, in, out, st);
+      case 3: return launch_strip<3>(p, in, out, st);
+      default: return launch_strip<4>(p, in, out, st);
+    }
   }
   const long long taps = (long long)(2 * p.wr + 1) * (2 * p.hr + 1);
   if (taps <= 64) return launch_group<8>(p, in, out, st);
