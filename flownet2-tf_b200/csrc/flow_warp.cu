@@ -4,8 +4,15 @@
 //   x2 = x + flow.x, y2 = y + flow.y; outside [0,W) x [0,H) (or NaN) -> 0; L = int(x2), T = int(y2),
 //   R = min(L+1, W-1), B = min(T+1, H-1); weights from alpha = x2-L, beta = y2-T.
 // Both kernels are HBM-bound gathers/scatters: one thread per pixel, the four tap weights in registers, flow read
-// as one 8-byte load, and (for the narrow images FlowNet2 warps, C <= 8) outputs staged through shared memory so
+// as one 8-byte load, and (for the narrow images FlowNet2 warps, C <= 4) outputs staged through shared memory so
 // the global stores are full 128-bit coalesced lines instead of C strided scalars.
+//
+// Narrow images, the tap access: the left and right taps of one image row are 2*C contiguous floats starting at a
+// 4-byte-aligned address.  Instead of 2*C scalar gathers (each a separate pass through L1 that touches up to 32
+// lines per warp) a thread reads the two or three ALIGNED 16-byte chunks that cover the span (LDG.128) and picks its
+// floats out of registers by the span's offset in the first chunk.  The backward scatters the same way: the 2*C
+// products are placed into chunk registers (zeros elsewhere, adding 0 is harmless) and sent as 16-byte vector
+// reductions (red.global.add.v4.f32), 2-3 per image row instead of 2*C scalar atomics.
 #include "fn2_common.cuh"
 
 namespace fn2 {
@@ -34,6 +41,84 @@ __device__ __forceinline__ Taps make_taps(float fx, float fy, int x, int y, int 
   return t;
 }
 
+
+// ---- aligned-chunk access to the 2*C floats [s, s + 2C) of a row pair (s = absolute float index in the tensor) ----
+template <int C>
+struct PairSpan {
+  static constexpr int NCH = (3 + 2 * C + 3) / 4;   // chunks that can be touched: offset <= 3
+};
+
+// value k (0 <= k < 4*NCH) of the chunk registers shifted by off: r[k + off]
+template <int NR>
+__device__ __forceinline__ float pick(const float (&r)[NR], int k, int off) {
+  const float a = r[k], b = (k + 1 < NR) ? r[k + 1] : 0.f, c = (k + 2 < NR) ? r[k + 2] : 0.f,
+              d = (k + 3 < NR) ? r[k + 3] : 0.f;
+  return off == 0 ? a : (off == 1 ? b : (off == 2 ? c : d));
+}
+
+template <int C>
+__device__ __forceinline__ void load_pair(const float* __restrict__ t, long long s, long long total, int len,
+                                          float (&v)[2 * C]) {
+  constexpr int NCH = PairSpan<C>::NCH;
+  const long long q = s >> 2;
+  const int off = (int)(s & 3);
+  float r[4 * NCH];
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    const long long f0 = (q + i) * 4;
+    float4 c4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (4 * i < off + len) {
+      if (f0 + 3 < total) {
+        c4 = __ldg(reinterpret_cast<const float4*>(t) + q + i);
+      } else {                                              // tail of a tensor whose size is not a multiple of 4
+        if (f0 < total) c4.x = __ldg(t + f0);
+        if (f0 + 1 < total) c4.y = __ldg(t + f0 + 1);
+        if (f0 + 2 < total) c4.z = __ldg(t + f0 + 2);
+      }
+    }
+    r[4 * i] = c4.x; r[4 * i + 1] = c4.y; r[4 * i + 2] = c4.z; r[4 * i + 3] = c4.w;
+  }
+#pragma unroll
+  for (int k = 0; k < 2 * C; ++k) v[k] = pick(r, k, off);
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// adds v[0 .. len) to t[s .. s + len): aligned 16-byte vector reductions, zeros in the lanes outside the span
+template <int C>
+__device__ __forceinline__ void scatter_pair(float* __restrict__ t, long long s, long long total, int len,
+                                             const float (&v)[2 * C]) {
+  constexpr int NCH = PairSpan<C>::NCH;
+  const long long q = s >> 2;
+  const int off = (int)(s & 3);
+  float r[4 * NCH];
+#pragma unroll
+  for (int k = 0; k < 4 * NCH; ++k) {
+    // r[k] = v[k - off] when that index is inside [0, len)
+    const float a = (k < 2 * C) ? v[k] : 0.f;
+    const float b = (k >= 1 && k - 1 < 2 * C) ? v[k - 1] : 0.f;
+    const float c = (k >= 2 && k - 2 < 2 * C) ? v[k - 2] : 0.f;
+    const float d = (k >= 3 && k - 3 < 2 * C) ? v[k - 3] : 0.f;
+    const float x = off == 0 ? a : (off == 1 ? b : (off == 2 ? c : d));
+    r[k] = (k - off < len) ? x : 0.f;
+  }
+#pragma unroll
+  for (int i = 0; i < NCH; ++i) {
+    if (4 * i < off + len) {
+      const long long f0 = (q + i) * 4;
+      if (f0 + 3 < total) {
+        red_add_v4(t + f0, r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (f0 + e < total && r[4 * i + e] != 0.f) atomicAdd(t + f0 + e, r[4 * i + e]);
+      }
+    }
+  }
+}
+
 // ---- forward, narrow images: thread per pixel, smem-staged coalesced stores -------------------------------
 template <int C>
 __global__ void __launch_bounds__(WARP_PIX) warp_fwd_narrow(const float* __restrict__ image,
@@ -52,16 +137,18 @@ __global__ void __launch_bounds__(WARP_PIX) warp_fwd_narrow(const float* __restr
     const float2 f = __ldg(flow + pix);
     const Taps t = make_taps(f.x, f.y, x, y, W, H);
     if (t.in) {
-      const float* img = image + (size_t)n * H * W * C;
-      const float* pTL = img + ((size_t)t.T * W + t.L) * C;
-      const float* pTR = img + ((size_t)t.T * W + t.R) * C;
-      const float* pBL = img + ((size_t)t.B * W + t.L) * C;
-      const float* pBR = img + ((size_t)t.B * W + t.R) * C;
+      const long long total = npix * C;
+      const int len = (t.R == t.L) ? C : 2 * C;            // right tap clamped onto the left one (:56)
+      float top[2 * C], bot[2 * C];
+      load_pair<C>(image, ((n * H + t.T) * (long long)W + t.L) * C, total, len, top);
+      load_pair<C>(image, ((n * H + t.B) * (long long)W + t.L) * C, total, len, bot);
       const float cTL = (1 - t.alpha) * (1 - t.beta), cTR = t.alpha * (1 - t.beta);
       const float cBL = (1 - t.alpha) * t.beta, cBR = t.alpha * t.beta;
 #pragma unroll
-      for (int c = 0; c < C; ++c)
-        v[c] = cTL * __ldg(pTL + c) + cTR * __ldg(pTR + c) + cBL * __ldg(pBL + c) + cBR * __ldg(pBR + c);
+      for (int c = 0; c < C; ++c) {
+        const float iTR = (t.R == t.L) ? top[c] : top[C + c], iBR = (t.R == t.L) ? bot[c] : bot[C + c];
+        v[c] = cTL * top[c] + cTR * iTR + cBL * bot[c] + cBR * iBR;
+      }
     }
   }
 #pragma unroll
@@ -176,17 +263,20 @@ __global__ void __launch_bounds__(WARP_PIX) warp_bwd_narrow(const float* __restr
 
   // ---- d/dflow (needs the four taps of the image) ----
   float2 gf = make_float2(0.f, 0.f);
-  const float* img = image + (size_t)n * H * W * C;
-  const size_t oTL = ((size_t)t.T * W + t.L) * C, oTR = ((size_t)t.T * W + t.R) * C;
-  const size_t oBL = ((size_t)t.B * W + t.L) * C, oBR = ((size_t)t.B * W + t.R) * C;
+  const long long total = npix * C;
+  const long long sT = ((n * H + t.T) * (long long)W + t.L) * C, sB = ((n * H + t.B) * (long long)W + t.L) * C;
+  const bool clampR = (t.R == t.L);
   if (act) {
     const float gy = float(t.B) - t.y2;  // flow_warp_grad.cu.cc:55
     const float gx = float(t.R) - t.x2;  // :72
+    float top[2 * C], bot[2 * C];
+    load_pair<C>(image, sT, total, clampR ? C : 2 * C, top);
+    load_pair<C>(image, sB, total, clampR ? C : 2 * C, bot);
     float bx = 0.f, by = 0.f;
 #pragma unroll
     for (int c = 0; c < C; ++c) {
-      const float iTL = __ldg(img + oTL + c), iTR = __ldg(img + oTR + c);
-      const float iBL = __ldg(img + oBL + c), iBR = __ldg(img + oBR + c);
+      const float iTL = top[c], iTR = clampR ? top[c] : top[C + c];
+      const float iBL = bot[c], iBR = clampR ? bot[c] : bot[C + c];
       float tx = gy * (iTR - iTL);
       tx += (1 - gy) * (iBR - iBL);
       bx += g[c] * tx;
@@ -198,7 +288,7 @@ __global__ void __launch_bounds__(WARP_PIX) warp_bwd_narrow(const float* __restr
   }
   if (live) gflow[pix] = gf;  // 8-byte coalesced store
 
-  // ---- d/dimage: neighbour aggregation, then atomics ----
+  // ---- d/dimage: neighbour aggregation, then vector reductions ----
   // key of my left column / right column targets (same image n within a warp unless the warp straddles images)
   const long long keyL = act ? ((n * H + t.T) * (long long)W + t.L) : -1;
   const long long keyR = act ? ((n * H + t.T) * (long long)W + t.R) : -2;
@@ -206,7 +296,7 @@ __global__ void __launch_bounds__(WARP_PIX) warp_bwd_narrow(const float* __restr
   // what the lane to my left would send to its right column
   const long long upKeyR = __shfl_up_sync(FULL, keyR, 1);
   const int upB = __shfl_up_sync(FULL, myB, 1);
-  const bool absorb = (lane > 0) && act && (upKeyR == keyL) && (upB == myB);
+  const bool absorb = (lane > 0) && act && !clampR && (upKeyR == keyL) && (upB == myB);
   // does the lane to my right absorb my right column?
   const bool given = __shfl_down_sync(FULL, absorb ? 1 : 0, 1) && (lane < 31);
 #pragma unroll
@@ -216,18 +306,23 @@ __global__ void __launch_bounds__(WARP_PIX) warp_bwd_narrow(const float* __restr
     if (absorb) { wTL[c] += upTR; wBL[c] += upBR; }
   }
   if (act) {
-    float* gi = gimage + (size_t)n * H * W * C;
+    // right taps that coincide with the left ones (clamped) or that the neighbour took over leave the span
+    const int len = (clampR || given) ? C : 2 * C;
+    float vt[2 * C], vb[2 * C];
 #pragma unroll
     for (int c = 0; c < C; ++c) {
-      atomicAdd(gi + oTL + c, wTL[c]);
-      atomicAdd(gi + oBL + c, wBL[c]);
+      vt[c] = wTL[c] + ((clampR && !given) ? wTR[c] : 0.f);
+      vb[c] = wBL[c] + ((clampR && !given) ? wBR[c] : 0.f);
+      vt[C + c] = wTR[c];
+      vb[C + c] = wBR[c];
     }
-    if (!given) {
+    if (t.B == t.T) {                                      // bottom taps clamped onto the top row (:57)
 #pragma unroll
-      for (int c = 0; c < C; ++c) {
-        atomicAdd(gi + oTR + c, wTR[c]);
-        atomicAdd(gi + oBR + c, wBR[c]);
-      }
+      for (int k = 0; k < 2 * C; ++k) vt[k] += vb[k];
+      scatter_pair<C>(gimage, sT, total, len, vt);
+    } else {
+      scatter_pair<C>(gimage, sT, total, len, vt);
+      scatter_pair<C>(gimage, sB, total, len, vb);
     }
   }
 }
