@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) corr_generic_fwd_kernel(CorrGeom g, const
   const int n = (int)(pix / ((long long)g.oW * g.oH));
   const int ya = yo * g.s1 + g.off, xa = xo * g.s1 + g.off;
   const float* an = a + (size_t)n * g.H * g.W * g.C;
-  const float* bn = b + (size_t)n * g.H * g.W * g.C;
+  const float* bn = b + (size_t)n * g.bH * g.W * g.C;   // b may carry row halos: its row = a-row + bTop
   const float sumelems = (float)(g.k * g.k * g.C);
   float* po = out + (size_t)pix * g.D;
 
@@ -55,8 +55,8 @@ __global__ void __launch_bounds__(256) corr_generic_fwd_kernel(CorrGeom g, const
       if (d < g.D) {
         const int s2o = (d % g.gw - g.r) * g.s2, s2p = (d / g.gw - g.r) * g.s2;
         for (int j = 0; j < g.k; ++j) {
-          const int y1 = ya + j, y2 = y1 + s2p;
-          if (y1 < 0 || y1 >= g.H || y2 < 0 || y2 >= g.H) continue;
+          const int y1 = ya + j, y2 = y1 + s2p + g.bTop;
+          if (y1 < 0 || y1 >= g.H || y2 < 0 || y2 >= g.bH) continue;
           for (int i = 0; i < g.k; ++i) {
             const int x1 = xa + i, x2 = x1 + s2o;
             if (x1 < 0 || x1 >= g.W || x2 < 0 || x2 >= g.W) continue;
@@ -83,25 +83,28 @@ __global__ void __launch_bounds__(256) corr_generic_fwd_kernel(CorrGeom g, const
   }
 }
 
-// One CTA per input pixel, threads over channels.  d/da and d/db in one pass, no atomics.
+// One CTA per pixel of the (possibly taller, row-halo) b-space, threads over channels.  d/da (when the pixel is also
+// a pixel of a) and d/db in one pass, no atomics.
 __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const float* __restrict__ gout,
                                                                const float* __restrict__ a,
                                                                const float* __restrict__ b, float* __restrict__ ga,
                                                                float* __restrict__ gb) {
-  const long long pix = blockIdx.x;  // n*H*W + yy*W + xx
+  const long long pix = blockIdx.x;  // n*bH*W + yb*W + xx
   const int xx = (int)(pix % g.W);
-  const int yy = (int)((pix / g.W) % g.H);
-  const int n = (int)(pix / ((long long)g.W * g.H));
+  const int ybrow = (int)((pix / g.W) % g.bH);
+  const int n = (int)(pix / ((long long)g.W * g.bH));
+  const int yy = ybrow - g.bTop;             // the same row in a's coordinates (outside [0,H) on halo rows)
+  const bool has_a = (yy >= 0) && (yy < g.H);
   const int x = xx + g.pad, y = yy + g.pad;  // padded coordinates
   const float* an = a + (size_t)n * g.H * g.W * g.C;
-  const float* bn = b + (size_t)n * g.H * g.W * g.C;
+  const float* bn = b + (size_t)n * g.bH * g.W * g.C;
   const float* gn = gout + (size_t)n * g.oH * g.oW * g.D;
   const float sumelems = (float)(g.k * g.k * g.C);
 
   // output range covering this element for d/da (same for every displacement)
   int axmin = ceil_div_s(x - 2 * g.kr - g.md, g.s1), aymin = ceil_div_s(y - 2 * g.kr - g.md, g.s1);
   int axmax = floor_div(x - g.md, g.s1), aymax = floor_div(y - g.md, g.s1);
-  const bool a_any = (axmax >= 0) && (aymax >= 0) && (axmin <= g.oW - 1) && (aymin <= g.oH - 1);
+  const bool a_any = has_a && (axmax >= 0) && (aymax >= 0) && (axmin <= g.oW - 1) && (aymin <= g.oH - 1);
   axmin = max(0, axmin); axmax = min(g.oW - 1, axmax);
   aymin = max(0, aymin); aymax = min(g.oH - 1, aymax);
 
@@ -112,8 +115,8 @@ __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const
         const int op = (p + g.r) * g.gw + (o + g.r);
         const int s2o = g.s2 * o, s2p = g.s2 * p;
         if (a_any) {
-          const int yb = y + s2p - g.pad, xb = x + s2o - g.pad;
-          if (yb >= 0 && yb < g.H && xb >= 0 && xb < g.W) {
+          const int yb = y + s2p - g.pad + g.bTop, xb = x + s2o - g.pad;
+          if (yb >= 0 && yb < g.bH && xb >= 0 && xb < g.W) {
             const float bv = __ldg(bn + ((size_t)yb * g.W + xb) * g.C + c);
             for (int y2 = aymin; y2 <= aymax; ++y2)
               for (int x2 = axmin; x2 <= axmax; ++x2)
@@ -137,7 +140,7 @@ __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const
         }
       }
     }
-    ga[(size_t)pix * g.C + c] = sa / sumelems;
+    if (has_a) ga[(((size_t)n * g.H + yy) * g.W + xx) * g.C + c] = sa / sumelems;
     gb[(size_t)pix * g.C + c] = sb / sumelems;
   }
 }
@@ -158,7 +161,7 @@ int corr_generic_forward(const CorrGeom& g, const float* a, const float* b, floa
 
 int corr_generic_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
                           float* gb, cudaStream_t st) {
-  const long long npix = (long long)g.N * g.H * g.W;
+  const long long npix = (long long)g.N * g.bH * g.W;
   if (npix > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   int threads = ((g.C + 31) / 32) * 32;
   if (threads > 256) threads = 256;

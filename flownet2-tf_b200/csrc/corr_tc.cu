@@ -12,6 +12,13 @@
 // the +-r window out of each TMEM row, restage it through shared memory and write the 441-channel output coalesced.
 // Zero padding is TMA out-of-bounds fill; b-rows outside the image are never loaded, their outputs are written as 0.
 //
+// Wide images (class width > 32, e.g. the 4K strips of cfg5): column tiles of 32 a-pixels need b-columns
+// x0-10 .. x0+41, so every group of 4 b-rows is visited as TWO 32-column blocks with origins x0-16 and x0+16 (negative
+// and past-the-edge coordinates are TMA zero fill = the op's padding); each (pixel, displacement) pair lives in
+// exactly one of the two, and each half has its own per-lane store plan.
+// Row halos (strip partitioning, fn2_correlation_forward_halo): b may be a taller tensor than a; a-row y meets b-rows
+// y + boff + p in class space, rows outside b are the op's zero padding.
+//
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = epilogue
 // (two warps per TMEM lane quadrant, taking alternate b-rows).
 #include "fn2_tc.cuh"
@@ -38,6 +45,8 @@ struct TcParams {
   float* out;
   int N, H, W, C, D, s2, ncls;
   int Hc[2], Wc[2];   // class-space extent per parity
+  int Hcb[2];         // class-space rows of b (>= Hc + boff when b carries row halos)
+  int boff;           // class-space row of b that a-row 0 meets at displacement 0 (halo_top / s2)
   int TY, TX;         // tiles per class (upper bound over classes)
   int nkc;            // C / 32
   float sumelems;
@@ -54,9 +63,12 @@ struct __align__(8) Barriers {
 
 
 // Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 16 KB][staging: NEPI x 32x33 floats][barriers]
-template <int R>
+template <int R, bool WIDE>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_constant__ TcParams P) {
   constexpr int GW = 2 * R + 1;
+  constexpr int NHX = WIDE ? 2 : 1;                 // 32-column b blocks per group of 4 b-rows
+  constexpr int XO0 = WIDE ? -16 : 0;               // column origin of the first one, relative to the a tile
+  constexpr int NTT = WIDE ? (GW * 16 + 31) / 32 : GW;  // store instructions per (a-row, b-row, block)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // keep shared-space provenance (plain LDS/STS, not generic LD/ST): index the array instead of casting through ints
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -77,9 +89,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
   const int Hc = P.Hc[cy], Wc = P.Wc[cx];
   const int y0 = ty * TILE_R, x0 = tx * TILE_C;
   if (y0 >= Hc || x0 >= Wc) return;  // whole CTA leaves together, before any barrier exists
-  const int s_first = max(0, y0 - R);
-  const int s_last = min(Hc - 1, y0 + TILE_R - 1 + R);
-  const int nblk = (s_last - s_first + 1 + 3) / 4;   // blocks of 4 b-rows (32 px each)
+  const int Hcb = P.Hcb[cy];
+  const int s_first = max(0, y0 + P.boff - R);
+  const int s_last = min(Hcb - 1, y0 + P.boff + TILE_R - 1 + R);
+  const int nblk = max(0, (s_last - s_first + 1 + 3) / 4) * NHX;   // blocks of 4 b-rows x 32 b-columns
   const int nkc = P.nkc;
 
   if (threadIdx.x == 0) {
@@ -104,13 +117,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
         tma_load_4d(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls], a_full, kc * KCH, x0, y0, n);
       int it = 0;
       for (int blk = 0; blk < nblk; ++blk) {
-        const int srow = s_first + blk * 4;
+        const int srow = s_first + (blk / NHX) * 4;
+        const int xcol = x0 + XO0 + (blk % NHX) * 32;
         for (int kc = 0; kc < nkc; ++kc, ++it) {
           const int stage = it % NSTAGE;
           mbar_wait(smem_u32(&bars->empty[stage]), ((it / NSTAGE) & 1) ^ 1);
           const uint32_t full = smem_u32(&bars->full[stage]);
           mbar_expect_tx(full, CHUNK_BYTES);
-          tma_load_4d(smem_u32(sB + (size_t)stage * CHUNK_BYTES), &P.b[cls], full, kc * KCH, x0, srow, n);
+          tma_load_4d(smem_u32(sB + (size_t)stage * CHUNK_BYTES), &P.b[cls], full, kc * KCH, xcol, srow, n);
         }
       }
     }
@@ -156,26 +170,49 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
     float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.D;
     const int pixstride = P.s2 * P.D;    // floats between neighbouring pixels of the class
 
-    // Per-lane plan for writing one displacement row (32 pixels x GW values, 84-byte runs) coalesced:
-    // element e = tt*32 + lane -> pixel cc = e / GW, displacement o = e % GW, source column xb = cc + o - R.
-    int rd[GW], gl[GW];
-    uint32_t xmask = 0, smask = 0;
+    // Per-lane plan for writing one displacement row (32 pixels x GW values, 84-byte runs) coalesced.
+    // Block hx covers b-columns [XO, XO + 32) relative to the tile (XO = XO0 + 32 * hx); pixel cc keeps from it the
+    // displacements o with 0 <= cc + o - R - XO < 32.  The kept (cc, o) pairs are enumerated pixel-major and dealt to
+    // the lanes 32 at a time: element e = tt*32 + lane.  !WIDE: every pair is enumerated (the ones whose b-column
+    // falls outside the single block are outside the image: written as zeros).
+    int rd[NHX][NTT], gl[NHX][NTT];
+    uint32_t xmask = 0, smask[NHX];
 #pragma unroll
-    for (int tt = 0; tt < GW; ++tt) {
-      const int e = tt * 32 + lane;
-      const int cc = e / GW, o = e - cc * GW;
-      const int xb = cc + o - R;
-      const bool xok = (xb >= 0) && (xb < 32);
-      rd[tt] = xok ? xb * 33 + cc : 0;
-      gl[tt] = cc * pixstride + o;
-      xmask |= (xok ? 1u : 0u) << tt;
-      smask |= ((cc < ncol) ? 1u : 0u) << tt;
+    for (int hx = 0; hx < NHX; ++hx) {
+      smask[hx] = 0;
+      const int XO = XO0 + 32 * hx;
+#pragma unroll
+      for (int tt = 0; tt < NTT; ++tt) {
+        const int e = tt * 32 + lane;
+        int cc, o;
+        bool live = true;
+        if (!WIDE) {
+          cc = e / GW; o = e - cc * GW;
+        } else {
+          // pixel cc keeps o in [lo, hi]; find the pixel whose run contains element e
+          int acc = 0; cc = 0; o = 0; live = false;
+#pragma unroll 1
+          for (int c2 = 0; c2 < 32; ++c2) {
+            const int lo = max(0, R + XO - c2), hi = min(GW - 1, R + XO + 31 - c2);
+            const int cnt = max(0, hi - lo + 1);
+            if (!live && e < acc + cnt) { cc = c2; o = lo + (e - acc); live = true; }
+            acc += cnt;
+          }
+        }
+        const int xb = cc + o - R - XO;
+        const bool xok = (xb >= 0) && (xb < 32);
+        rd[hx][tt] = xok ? xb * 33 + cc : 0;
+        gl[hx][tt] = cc * pixstride + o;
+        if (hx == 0) xmask |= (xok ? 1u : 0u) << tt;
+        smask[hx] |= ((live && cc < ncol) ? 1u : 0u) << tt;
+      }
     }
 
     // displacement rows that point outside the image: written as zeros here, never computed
     if (row_ok) {
-      const int dlo = max(0, R - y) * GW;                 // p < -y
-      const int dhi = min(GW, Hc - y + R) * GW;           // p > Hc-1-y
+      const int yb = y + P.boff;                          // b-row this a-row meets at p = 0
+      const int dlo = min(GW, max(0, R - yb)) * GW;       // p < -yb
+      const int dhi = max(0, min(GW, Hcb - yb + R)) * GW; // p > Hcb-1-yb
       for (int cc = half; cc < ncol; cc += 2) {
         float* po = orow0 + (size_t)cc * pixstride;
         for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
@@ -183,34 +220,38 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
       }
     }
 
-    for (int blk = 0; blk < nblk; ++blk) {
-      const int buf = blk % NBUF;
-      mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
-      tc_fence_after();
+    for (int blk0 = 0; blk0 < nblk; blk0 += NHX) {
 #pragma unroll
-      for (int h2 = 0; h2 < 2; ++h2) {
-        const int br = half + 2 * h2;
-        const int s = s_first + blk * 4 + br;
-        const int p = s - y;
-        if (row_ok && p >= -R && p <= R && s < Hc) {   // warp-uniform
-          float v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
+      for (int hx = 0; hx < NHX; ++hx) {
+        const int blk = blk0 + hx;
+        const int buf = blk % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
+        tc_fence_after();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
-          __syncwarp();
-          float* orow = orow0 + (p + R) * GW;
+        for (int h2 = 0; h2 < 2; ++h2) {
+          const int br = half + 2 * h2;
+          const int s = s_first + (blk0 / NHX) * 4 + br;
+          const int p = s - (y + P.boff);
+          if (row_ok && p >= -R && p <= R && s < Hcb) {   // warp-uniform
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
 #pragma unroll
-          for (int tt = 0; tt < GW; ++tt) {
-            float x = stg[rd[tt]];
-            x = ((xmask >> tt) & 1u) ? x * inv : 0.f;
-            if ((smask >> tt) & 1u) orow[gl[tt]] = x;
+            for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+            __syncwarp();
+            float* orow = orow0 + (p + R) * GW;
+#pragma unroll
+            for (int tt = 0; tt < NTT; ++tt) {
+              float x = stg[rd[hx][tt]];
+              x = (WIDE || ((xmask >> tt) & 1u)) ? x * inv : 0.f;
+              if ((smask[hx] >> tt) & 1u) orow[gl[hx][tt]] = x;
+            }
+            __syncwarp();
           }
-          __syncwarp();
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
     }
   }
 
@@ -235,8 +276,7 @@ bool corr_tc_supported(const CorrGeom& g, int precision) {
   if (g.s2 != 1 && g.s2 != 2) return false;
   if (g.r != 10) return false;                       // window radius instantiated below
   if (g.C % KCH != 0 || g.C / KCH > MAX_KC) return false;
-  const int Wc0 = (g.W + g.s2 - 1) / g.s2;
-  if (Wc0 > TILE_C) return false;                    // single column tile for now (cfg1/cfg3 shapes)
+  if (g.bTop % g.s2 != 0) return false;              // a row halo must keep the parity classes aligned
   return true;
 }
 
@@ -248,9 +288,11 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   TcParams P;
   P.out = out;
   P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
+  P.boff = g.bTop / g.s2;
   for (int c = 0; c < 2; ++c) {
     P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
     P.Wc[c] = c < g.s2 ? (g.W - c + g.s2 - 1) / g.s2 : 0;
+    P.Hcb[c] = c < g.s2 ? (g.bH - c + g.s2 - 1) / g.s2 : 0;
   }
   P.TY = (P.Hc[0] + TILE_R - 1) / TILE_R;
   P.TX = (P.Wc[0] + TILE_C - 1) / TILE_C;
@@ -263,7 +305,7 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
       continue;
     }
     if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, TILE_R) ||
-        !make_class_map(&P.b[cls], b, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, 4))
+        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 4))
       return FN2_E_CUDA;
   }
   for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }
@@ -271,13 +313,19 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)fwd_smem_bytes(MAX_KC));
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)fwd_smem_bytes(MAX_KC));
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
-  corr_tc_fwd_kernel<10><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  if (P.TX > 1)
+    corr_tc_fwd_kernel<10, true><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  else
+    corr_tc_fwd_kernel<10, false><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   return after_launch();
 }
 

@@ -21,6 +21,12 @@
 //     last source row the same eight warps read it back (lane = channel) and store 128-byte channel runs.
 // CTAs of the two modes for the same image are adjacent in the grid so the second read of `gradients` hits L2.
 //
+// Wide images (class width > 32): output tiles are 32 columns wide and need source columns x0-10 .. x0+41, so each
+// source row is visited as two 32-pixel items with origins x0-16 and x0+16 (TMA zero fill outside the image).
+// Row halos (strip partitioning, fn2_correlation_backward_halo): b and db may be taller than a; a-row y meets b-rows
+// y + boff + p in class space.  db is produced for every row of the tall tensor (halo rows = the partial sums the
+// neighbouring strip adds to its own).
+//
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = G builders, then
 // epilogue.
 #include "fn2_tc.cuh"
@@ -47,7 +53,10 @@ struct BwdParams {
   float* out[2];        // da, db
   int N, H, W, C, D, s2, ncls, R, GW;
   int Hc[2], Wc[2];
-  int TY;
+  int Hcb[2];           // class-space rows of b / db (>= Hc + boff with row halos)
+  int bH;               // full-resolution rows of b / db
+  int boff;             // class-space row of b that a-row 0 meets at displacement 0
+  int TY, TX;
   int nchunk;           // C / 32
   int nhalf;            // ceil(C / 128)
   float inv;            // 1 / C
@@ -77,21 +86,41 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // ---- which tile: ((n * ncls + cls) * TY + ty) * 2 + mode ----
+  // ---- which tile: (((n * ncls + cls) * TY + ty) * TX + tx) * 2 + mode ----
   int t = blockIdx.x;
   const int mode = t & 1; t >>= 1;
+  const int tx = t % P.TX; t /= P.TX;
   const int ty = t % P.TY; t /= P.TY;
   const int cls = t % P.ncls;
   const int n = t / P.ncls;
   const int cy = cls / P.s2, cx = cls % P.s2;
-  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
-  const int r0 = ty * TILE_R;
-  if (r0 >= Hc || Wc < 1) return;  // whole CTA leaves together, before any barrier exists
+  const int Wc = P.Wc[cx];
+  const int Hout = mode ? P.Hcb[cy] : P.Hc[cy];   // class rows of the output tensor (da: a-space, db: b-space)
+  const int Hsrc = mode ? P.Hc[cy] : P.Hcb[cy];   // class rows of the streamed tensor
+  const int Ha = P.Hc[cy];
+  const int r0 = ty * TILE_R, x0 = tx * TILE_C;
+  if (r0 >= Hout || x0 >= Wc) return;  // whole CTA leaves together, before any barrier exists
   const int R = P.R;
-  const int t_first = max(0, r0 - R);
-  const int t_last = min(Hc - 1, r0 + TILE_R - 1 + R);
+  // output row ro meets source rows ro + shift - R .. ro + shift + R  (shift = +boff for da, -boff for db)
+  const int shift = mode ? -P.boff : P.boff;
+  const int t_first = max(0, r0 + shift - R);
+  const int t_last = min(Hsrc - 1, r0 + TILE_R - 1 + shift + R);
   const int nrows = t_last - t_first + 1;
   const int nchunk = P.nchunk;
+  const int nhx = P.TX > 1 ? 2 : 1;               // 32-pixel source items per source row
+  const int nitems = nrows * nhx;
+  const int ncol = min(TILE_C, Wc - x0);
+  float* const outp = P.out[mode];
+  const int Hfull = mode ? P.bH : P.H;            // full-resolution rows of the output tensor
+  if (nrows <= 0) {  // no source row reaches this tile (halo deeper than the displacement range): zeros
+    for (int qq = 0; qq < TILE_R; ++qq) {
+      const int row = r0 + qq;
+      if (row >= Hout) break;
+      float* orow = outp + (((size_t)n * Hfull + (size_t)(row * P.s2 + cy)) * P.W + cx + (size_t)x0 * P.s2) * P.C;
+      for (int e = threadIdx.x; e < ncol * P.C; e += NTHREADS) orow[(size_t)(e / P.C) * P.s2 * P.C + e % P.C] = 0.f;
+    }
+    return;
+  }
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NST; ++i) {
@@ -113,13 +142,15 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
     // ================================ TMA producer: one source row of X per stage ================================
     if (lane == 0) {
       const CUtensorMap* map = &P.x[mode][cls];
-      for (int it = 0; it < nrows; ++it) {
+      for (int it = 0; it < nitems; ++it) {
         const int stage = it % NST;
+        const int row = t_first + it / nhx;
+        const int xs0 = nhx > 1 ? x0 - 16 + 32 * (it % nhx) : 0;
         mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
         const uint32_t full = smem_u32(&bars->x_full[stage]);
         mbar_expect_tx(full, (uint32_t)nchunk * XCHUNK);
         for (int c = 0; c < nchunk; ++c)
-          tma_load_4d(smem_u32(sX + (size_t)stage * XSTAGE + (size_t)c * XCHUNK), map, full, c * KCH, 0, t_first + it, n);
+          tma_load_4d(smem_u32(sX + (size_t)stage * XSTAGE + (size_t)c * XCHUNK), map, full, c * KCH, xs0, row, n);
       }
     }
   } else if (warp == 1) {
@@ -129,7 +160,7 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
       // B = G  : mode 0 K-major (N = a-pixel rows, K = b-pixel cols); mode 1 MN-major (N = b-pixel cols, LBO = block
       //          stride, K = a-pixel rows).
       const uint32_t idesc = idesc_tf32_major(128, 128, 1, mode);
-      for (int it = 0; it < nrows; ++it) {
+      for (int it = 0; it < nitems; ++it) {
         const int stage = it % NST;
         const uint32_t par = (it / NST) & 1;
         mbar_wait(smem_u32(&bars->x_full[stage]), par);
@@ -157,21 +188,27 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
     const int xh = (bw & 1) * 16;     // this warp fills a-pixel rows xh .. xh+15 of the block
     const int GW = P.GW;
     const int xb = lane;              // column of the block = b-pixel
-    for (int it = 0; it < nrows; ++it) {
+    for (int it = 0; it < nitems; ++it) {
       const int stage = it % NST;
-      const int tt = t_first + it;
-      // a-row and displacement row of this block for this source row
+      const int tt = t_first + it / nhx;
+      const int xs0 = nhx > 1 ? x0 - 16 + 32 * (it % nhx) : 0;
+      // a-row and displacement row of this block for this source row: b-row = a-row + boff + p
       const int ya = mode ? tt : r0 + q;
-      const int p = mode ? (r0 + q - tt) : (tt - (r0 + q));
-      const bool blk_ok = (ya < Hc) && (r0 + q < Hc) && (p >= -R) && (p <= R);
+      const int p = mode ? (r0 + q - P.boff - tt) : (tt - P.boff - (r0 + q));
+      const bool blk_ok = (ya < Ha) && (r0 + q < Hout) && (p >= -R) && (p <= R);
+      // block rows are a-pixels, block columns are b-pixels; the tile owns the a-columns for da, the b-columns for db
+      const int a0 = mode ? xs0 : x0, b0 = mode ? x0 : xs0;
+      const int babs = b0 + xb;
       float v[16];
-      const float* grow = P.grad + (((size_t)n * P.H + (size_t)(ya * P.s2 + cy)) * P.W + cx) * P.D + (p + R) * GW;
+      const float* grow = P.grad + (((size_t)n * P.H + (size_t)((blk_ok ? ya : 0) * P.s2 + cy)) * P.W + cx) * P.D +
+                          (p + R) * GW;
 #pragma unroll
       for (int rr = 0; rr < 16; ++rr) {
         const int x = xh + rr;
-        const int o = xb - x + R;
-        const bool ok = blk_ok && (x < Wc) && (xb < Wc) && (o >= 0) && (o < GW);
-        v[rr] = ok ? __ldg(grow + (size_t)x * P.s2 * P.D + o) : 0.f;
+        const int aabs = a0 + x;
+        const int o = babs - aabs + R;
+        const bool ok = blk_ok && (aabs >= 0) && (aabs < Wc) && (babs >= 0) && (babs < Wc) && (o >= 0) && (o < GW);
+        v[rr] = ok ? __ldg(grow + (ptrdiff_t)aabs * P.s2 * P.D + o) : 0.f;
       }
       mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
       uint8_t* blk = sG + (size_t)stage * GSTAGE + (size_t)q * GBLOCK;
@@ -194,17 +231,15 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
     tc_fence_after();
     const int qd = warp & 3;        // TMEM lane quadrant this warp may read
     const int e = bw >> 2;          // the two warps of a quadrant take alternate output rows
-    float* outp = P.out[mode];
-    const int ncol = min(TILE_C, Wc);
     const float inv = P.inv;
     for (int h = 0; h < P.nhalf; ++h) {
       const int ch = h * 128 + qd * 32 + lane;
       for (int qq = e; qq < TILE_R; qq += 2) {
         const int row = r0 + qq;
-        if (row >= Hc) continue;    // warp-uniform
+        if (row >= Hout) continue;  // warp-uniform
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * 128 + qq * 32), v);
-        float* orow = outp + (((size_t)n * P.H + (size_t)(row * P.s2 + cy)) * P.W + cx) * P.C + ch;
+        float* orow = outp + (((size_t)n * Hfull + (size_t)(row * P.s2 + cy)) * P.W + cx + (size_t)x0 * P.s2) * P.C + ch;
         if (ch < P.C) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
@@ -231,8 +266,7 @@ bool corr_tc_bwd_supported(const CorrGeom& g, int precision) {
   if (g.k != 1 || g.s1 != 1 || g.pad != g.md) return false;
   if (g.s2 != 1 && g.s2 != 2) return false;
   if (g.C % KCH != 0 || g.C / KCH > MAX_CH) return false;
-  const int Wc0 = (g.W + g.s2 - 1) / g.s2;
-  if (Wc0 > TILE_C) return false;  // single column tile for now (cfg1/cfg3 shapes)
+  if (g.bTop % g.s2 != 0) return false;
   return true;
 }
 
@@ -244,11 +278,14 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
   P.out[0] = ga; P.out[1] = gb;
   P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
   P.R = g.r; P.GW = g.gw;
+  P.bH = g.bH; P.boff = g.bTop / g.s2;
   for (int c = 0; c < 2; ++c) {
     P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
     P.Wc[c] = c < g.s2 ? (g.W - c + g.s2 - 1) / g.s2 : 0;
+    P.Hcb[c] = c < g.s2 ? (g.bH - c + g.s2 - 1) / g.s2 : 0;
   }
-  P.TY = (P.Hc[0] + TILE_R - 1) / TILE_R;
+  P.TY = (P.Hcb[0] + TILE_R - 1) / TILE_R;   // db tiles cover the (possibly taller) b-space
+  P.TX = (P.Wc[0] + TILE_C - 1) / TILE_C;
   P.nchunk = g.C / KCH;
   P.nhalf = (g.C + 127) / 128;
   P.inv = 1.0f / (float)g.C;
@@ -256,11 +293,13 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
     const float* src = mode ? a : b;
     for (int cls = 0; cls < 4; ++cls) {
       const int cy = cls / g.s2, cx = cls % g.s2;
-      if (cls >= P.ncls || P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // unused / empty class: any valid map, never dereferenced
+      const int srcH = mode ? g.H : g.bH;
+      const int srcHc = mode ? P.Hc[cy] : P.Hcb[cy];
+      if (cls >= P.ncls || srcHc < 1 || P.Wc[cx] < 1) {  // unused / empty class: any valid map, never dereferenced
         P.x[mode][cls] = P.x[mode][0];
         continue;
       }
-      if (!make_class_map(&P.x[mode][cls], src, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, 1,
+      if (!make_class_map(&P.x[mode][cls], src, g.N, srcH, g.W, g.C, g.s2, cy, cx, srcHc, P.Wc[cx], TILE_C, 1,
                           CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
         return FN2_E_CUDA;
     }
@@ -273,7 +312,7 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
     attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
-  const long long grid = (long long)g.N * P.ncls * P.TY * 2;
+  const long long grid = (long long)g.N * P.ncls * P.TY * P.TX * 2;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   kern<<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   return after_launch();

@@ -41,6 +41,20 @@ static int make_geom(int N, int H, int W, int C, int k, int md, int s1, int s2, 
   g->gw = g->r * 2 + 1;
   g->D = g->gw * g->gw;
   g->off = md - pad;
+  g->bH = H;
+  g->bTop = 0;
+  return FN2_OK;
+}
+
+// Strip geometry: only the FlowNetC-type call (k == 1, s1 == 1, pad == md, so out rows == a
+// rows) can be cut into row strips with a halo of b; a halo that is not a multiple of stride_2 would misalign the
+// displacement grid.
+static int add_halo(CorrGeom* g, int halo_top, int halo_bottom) {
+  if (halo_top < 0 || halo_bottom < 0) return FN2_E_BAD_PARAM;
+  if (g->k != 1 || g->s1 != 1 || g->pad != g->md) return FN2_E_UNSUPPORTED_GEOMETRY;
+  if (halo_top % g->s2 != 0) return FN2_E_UNSUPPORTED_GEOMETRY;
+  g->bTop = halo_top;
+  g->bH = g->H + halo_top + halo_bottom;
   return FN2_OK;
 }
 
@@ -66,6 +80,8 @@ const char* fn2_error_string(int status) {
     case FN2_E_DOWNSAMPLE_SIZE: return "downsample output height and width must be >= 2";
     case FN2_E_CUDA: return "CUDA error; see fn2_last_cuda_error";
     case FN2_E_NO_DEVICE: return "no sm_100 CUDA device is current";
+    case FN2_E_UNSUPPORTED_GEOMETRY:
+      return "row halos need kernel_size 1, stride_1 1, pad == max_displacement and halo_top % stride_2 == 0";
     default: return "unknown fn2 status";
   }
 }
@@ -93,17 +109,47 @@ size_t fn2_correlation_workspace_bytes(int N, int H, int W, int C, int k, int md
   return corr_tc_workspace_bytes(g, precision, direction);
 }
 
+static int correlation_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void* ws,
+                               size_t ws_bytes, void* stream);
+static int correlation_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
+                                float* gb, int precision, void* ws, size_t ws_bytes, void* stream);
+
 int fn2_correlation_forward(const float* a, const float* b, float* out, int N, int H, int W, int C, int k, int md,
                             int s1, int s2, int pad, int precision, void* ws, size_t ws_bytes, void* stream) {
   CorrGeom g;
   const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
   if (rc != FN2_OK) return rc;
+  return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
+}
+
+int fn2_correlation_forward_halo(const float* a, const float* b, float* out, int N, int H, int W, int C, int k, int md,
+                                 int s1, int s2, int pad, int halo_top, int halo_bottom, int precision, void* ws,
+                                 size_t ws_bytes, void* stream) {
+  CorrGeom g;
+  int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc == FN2_OK) rc = add_halo(&g, halo_top, halo_bottom);
+  if (rc != FN2_OK) return rc;
+  return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
+}
+
+int fn2_correlation_backward_halo(const float* gout, const float* a, const float* b, float* ga, float* gb, int N,
+                                  int H, int W, int C, int k, int md, int s1, int s2, int pad, int halo_top,
+                                  int halo_bottom, int precision, void* ws, size_t ws_bytes, void* stream) {
+  CorrGeom g;
+  int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc == FN2_OK) rc = add_halo(&g, halo_top, halo_bottom);
+  if (rc != FN2_OK) return rc;
+  return correlation_backward(g, gout, a, b, ga, gb, precision, ws, ws_bytes, stream);
+}
+
+static int correlation_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void* ws,
+                               size_t ws_bytes, void* stream) {
   if (!a || !b || !out || !aligned16(a) || !aligned16(b) || !aligned16(out)) return FN2_E_BAD_POINTER;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (precision) {
     case FN2_PREC_FP32:
       if (corr_simt_supported(g)) return corr_simt_forward(g, a, b, out, st);
-      return corr_generic_forward(g, a, b, out, st);
+      return corr_generic_forward(g, a, b, out, st);   // handles row halos too
     case FN2_PREC_TF32:
     case FN2_PREC_BF16:
     case FN2_PREC_TF32X3:
@@ -121,6 +167,11 @@ int fn2_correlation_backward(const float* gout, const float* a, const float* b, 
   CorrGeom g;
   const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
   if (rc != FN2_OK) return rc;
+  return correlation_backward(g, gout, a, b, ga, gb, precision, ws, ws_bytes, stream);
+}
+
+static int correlation_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
+                                float* gb, int precision, void* ws, size_t ws_bytes, void* stream) {
   if (!gout || !a || !b || !ga || !gb) return FN2_E_BAD_POINTER;
   if (!aligned16(gout) || !aligned16(a) || !aligned16(b) || !aligned16(ga) || !aligned16(gb)) return FN2_E_BAD_POINTER;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

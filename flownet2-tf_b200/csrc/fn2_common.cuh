@@ -17,6 +17,9 @@ struct CorrGeom {
   int k, md, s1, s2, pad;
   int kr, oH, oW, r, gw, D;
   int off;  // unpadded coordinate of output (0,0)'s patch corner: md - pad
+  // Row halos (fn2_correlation_*_halo, strip partitioning): input_b / backprops_b have bH >= H rows and row y of
+  // input_a lines up with row y + bTop of input_b.  Plain calls: bH == H, bTop == 0.
+  int bH, bTop;
 };
 
 // Records a launch for fn2_launch_count() and returns the status of the launch that was just made.

@@ -45,7 +45,9 @@ typedef enum fn2_status {
   FN2_E_DOWNSAMPLE_SIZE = -9,  /* output height or width < 2: the reference divides by zero there
                                   (downsample_kernel_gpu.cu.cc:40-41,92-93); rejected instead           */
   FN2_E_CUDA = -10,            /* a CUDA runtime/driver call failed; see fn2_last_cuda_error()          */
-  FN2_E_NO_DEVICE = -11        /* no sm_100 device is current                                           */
+  FN2_E_NO_DEVICE = -11,       /* no sm_100 device is current                                           */
+  FN2_E_UNSUPPORTED_GEOMETRY = -12 /* *_halo entry points: need kernel_size 1, stride_1 1, pad == max_displacement,
+                                  halo_top a multiple of stride_2                                       */
 } fn2_status;
 
 /* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode. */
@@ -91,6 +93,30 @@ FN2_API int fn2_correlation_backward(const float* gradients, const float* input_
                              float* backprops_b, int N, int H, int W, int C, int kernel_size, int max_displacement,
                              int stride_1, int stride_2, int pad, int precision, void* workspace,
                              size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Row-strip variants (4K inputs cut into horizontal strips, one per GPU).  The reference has
+ * no such entry point: its CorrelationKernel::Compute (correlation_kernel.cc:13-136) always sees whole images; these
+ * compute exactly the rows of that result which belong to one strip.
+ *
+ *   input_a, output, gradients, backprops_a : the strip's own H rows
+ *   input_b, backprops_b                    : H + halo_top + halo_bottom rows; row y of input_a lines up with row
+ *                                             y + halo_top of input_b.  Rows beyond either end of input_b are the op's
+ *                                             zero padding (a strip at the image border passes halo 0 on that side).
+ * backprops_b is written for ALL rows of the tall tensor: its halo rows are the partial sums that belong to the
+ * neighbouring strips (the caller sends them back and adds them).  Requires kernel_size 1, stride_1 1,
+ * pad == max_displacement (FlowNetC's call, flownet_c.py:40) and halo_top % stride_2 == 0.
+ * --------------------------------------------------------------------------------------------------------- */
+FN2_API int fn2_correlation_forward_halo(const float* input_a, const float* input_b, float* output, int N, int H, int W,
+                                 int C, int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
+                                 int halo_top, int halo_bottom, int precision, void* workspace,
+                                 size_t workspace_bytes, void* stream);
+
+FN2_API int fn2_correlation_backward_halo(const float* gradients, const float* input_a, const float* input_b,
+                                  float* backprops_a, float* backprops_b, int N, int H, int W, int C,
+                                  int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
+                                  int halo_top, int halo_bottom, int precision, void* workspace,
+                                  size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * FlowWarp.  Replaces REGISTER_OP("FlowWarp") + FlowWarpKernel<GPUDevice>::Compute

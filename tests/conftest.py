@@ -69,3 +69,32 @@ def assert_close(got, want, rel=1e-5, abs_=1e-6, what=""):
     bad = err > lim
     assert not bad.any(), "%s: %d/%d outside tolerance, max err %.3e (limit there %.3e)" % (
         what, int(bad.sum()), bad.size, float(err.max()), float(lim.flat[int(err.argmax())]))
+
+
+# ---- oracle for the row-halo (strip) variants: the full op on zero-extended tensors, cropped -------------------
+def oracle_halo_forward(a, b_ext, k, md, s1, s2, pad, top, bottom, precision=None):
+    """numpy/torch-CPU restatement of fn2_correlation_forward_halo: extend a with zero rows to b_ext's height, run
+    the whole-image oracle, keep the strip's rows."""
+    import torch
+    from oracle import oracle as o
+    a_np = a.detach().cpu().numpy()
+    N, H, W, C = a_np.shape
+    a_ext = np.zeros((N, H + top + bottom, W, C), np.float32)
+    a_ext[:, top:top + H] = a_np
+    full = o.c_correlation(a_ext, np.ascontiguousarray(b_ext.detach().cpu().numpy()), k, md, s1, s2, pad, f64=True)
+    return torch.from_numpy(np.ascontiguousarray(full[:, top:top + H]).astype(np.float32))
+
+
+def oracle_halo_backward(g, a, b_ext, k, md, s1, s2, pad, top, bottom, precision=None):
+    import torch
+    from oracle import oracle as o
+    a_np, g_np = a.detach().cpu().numpy(), g.detach().cpu().numpy()
+    N, H, W, C = a_np.shape
+    a_ext = np.zeros((N, H + top + bottom, W, C), np.float32)
+    a_ext[:, top:top + H] = a_np
+    g_ext = np.zeros((N, H + top + bottom) + g_np.shape[2:], np.float32)
+    g_ext[:, top:top + H] = g_np
+    ga, gb = o.c_correlation_grad(g_ext, a_ext, np.ascontiguousarray(b_ext.detach().cpu().numpy()), k, md, s1, s2,
+                                  pad, f64=True)
+    return (torch.from_numpy(np.ascontiguousarray(ga[:, top:top + H]).astype(np.float32)),
+            torch.from_numpy(gb.astype(np.float32)))

@@ -1,0 +1,93 @@
+"""GPU parity of the row-halo (strip) entry points and of the wide-image tensor-core tiling (cfg5 shapes, scaled down
+so the oracle finishes in seconds).  One process plays every rank in turn: the exchange itself is covered on CPU by
+tests/test_strips_gloo.py; here the kernels behind fn2_correlation_{forward,backward}_halo are checked."""
+import numpy as np
+import pytest
+import torch
+
+import flownet2_tf_b200 as fn2
+from flownet2_tf_b200 import strips
+from oracle import oracle as o
+from conftest import assert_close, corr_inputs, grad_like
+
+pytestmark = pytest.mark.gpu
+
+ARGS = (1, 20, 1, 2, 20)
+TF32_TOL = 2.5e-3
+
+
+def _check(got, want, precision, what):
+    got = got.detach().cpu().numpy().astype(np.float64)
+    if precision == "fp32":
+        assert_close(got, want, what=what)
+    else:
+        err = np.abs(got - want).max() / max(np.abs(want).max(), 1e-30)
+        assert err <= TF32_TOL, "%s: %.3e of max" % (what, err)
+
+
+@pytest.mark.parametrize("shape", [(1, 20, 150, 64), (2, 9, 66, 32), (1, 30, 97, 256), (1, 6, 480, 32)])
+def test_wide_images_tf32(shape):
+    """class width > 32: several column tiles, two 32-column b blocks per row group (corr_tc.cu / corr_tc_bwd.cu)."""
+    N, H, W, C = shape
+    a, b = corr_inputs(N, H, W, C)
+    ad, bd = a.cuda().requires_grad_(), b.cuda().requires_grad_()
+    out = fn2.correlation(ad, bd, *ARGS, precision="tf32")
+    g = grad_like(out.shape)
+    out.backward(g.cuda())
+    _check(out, o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True), "tf32", "forward")
+    wga, wgb = o.c_correlation_grad(g.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
+    _check(ad.grad, wga, "tf32", "backprops_a")
+    _check(bd.grad, wgb, "tf32", "backprops_b")
+
+
+def test_wide_exact_on_integer_inputs():
+    N, H, W, C = 1, 12, 200, 32
+    g = torch.Generator().manual_seed(7)
+    a = torch.randint(-4, 5, (N, H, W, C), generator=g).float()
+    b = torch.randint(-4, 5, (N, H, W, C), generator=g).float()
+    out = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    np.testing.assert_array_equal(out.cpu().numpy().astype(np.float64),
+                                  o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True))
+    go = torch.randint(-4, 5, out.shape, generator=g).float()
+    ga, gb = fn2.correlation_grad(go.cuda(), a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    wga, wgb = o.c_correlation_grad(go.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
+    np.testing.assert_array_equal(ga.cpu().numpy().astype(np.float64), wga)
+    np.testing.assert_array_equal(gb.cpu().numpy().astype(np.float64), wgb)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("world,H,W,C", [(2, 44, 40, 32), (3, 70, 90, 64), (4, 96, 24, 32)])
+def test_strips_match_whole_image(precision, world, H, W, C):
+    a, b = corr_inputs(1, H, W, C)
+    g = grad_like((1, H, W, 441))
+    want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
+    wga, wgb = o.c_correlation_grad(g.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
+    h = strips.halo_rows(20, 2)
+    edges = [round(i * H / world) for i in range(world + 1)]
+    out = torch.empty(1, H, W, 441)
+    ga = torch.empty(1, H, W, C)
+    gb = torch.zeros(1, H, W, C)
+    for r in range(world):
+        y0, y1 = edges[r], edges[r + 1]
+        top, bottom = (h if r > 0 else 0), (h if r < world - 1 else 0)
+        a_s = a[:, y0:y1].contiguous().cuda()
+        b_ext = b[:, y0 - top:y1 + bottom].contiguous().cuda()
+        out[:, y0:y1] = strips.correlation_halo_forward(a_s, b_ext, *ARGS, top, bottom, precision).cpu()
+        ga_s, gb_ext = strips.correlation_halo_backward(g[:, y0:y1].contiguous().cuda(), a_s, b_ext, *ARGS, top,
+                                                        bottom, precision)
+        ga[:, y0:y1] = ga_s.cpu()
+        gb[:, y0 - top:y1 + bottom] += gb_ext.cpu()      # what the mirror exchange + add does
+    _check(out, want, precision, "forward")
+    _check(ga, wga, precision, "backprops_a")
+    _check(gb, wgb, precision, "backprops_b")
+
+
+def test_halo_entry_points_reject_other_geometries():
+    a = torch.zeros(1, 8, 8, 32, device="cuda")
+    b = torch.zeros(1, 12, 8, 32, device="cuda")
+    with pytest.raises(ValueError, match="row halos need"):
+        strips.correlation_halo_forward(a, b, 3, 20, 1, 2, 20, 2, 2, "fp32")     # kernel_size 3
+    with pytest.raises(ValueError, match="row halos need"):
+        strips.correlation_halo_forward(a, torch.zeros(1, 11, 8, 32, device="cuda"), 1, 20, 1, 2, 20, 3, 0, "fp32")
+    with pytest.raises(ValueError, match="input_b must have shape"):
+        strips.correlation_halo_forward(a, b, 1, 20, 1, 2, 20, 2, 0, "fp32")
