@@ -34,10 +34,11 @@ HI, WI = 384, 512
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("FN2_BENCH_PRECISION", "auto"))
+    ap.add_argument("--eager", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--batch", type=int, default=32, help="image pairs per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -166,7 +167,8 @@ def workload_config(batch, precision):
                         "[%d,48,64,256]->[%d,48,64,441] (k=1,d=20,s1=1,s2=2,pad=20) + flow_warp fwd+bwd "
                         "[%d,384,512,3] + downsample of GT flow to 5 loss scales" % (batch, batch, batch, batch),
             "pairs_per_gpu": batch, "correlation_precision": precision, "parallelism": "batch-sharded replicas",
-            "l2": "inputs larger than L2 (1.6 GB per step vs 126 MB)"}
+            "l2": "inputs larger than L2 (1.6 GB per step vs 126 MB)",
+            "launch": "CUDA graph replay per op, 5 per step (eager launches with --eager)"}
 
 
 # ------------------------------------------------------------------------------------------------------ ours
@@ -195,7 +197,8 @@ def main():
 
     precision = args.precision
     if precision == "auto":
-        precision = "fp32"
+        # the tcgen05 path is the one BASELINE.json's target is stated for; its tolerance is in tests/test_gpu_tc.py
+        precision = "tf32"
     B = args.batch
     host = host_data(B, seed=rank)
     a, b, g, image, flow, gimg, gt = [x.to(dev) for x in host]
@@ -223,71 +226,138 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
         step()
     barrier()
 
+    # Each op of the step is captured as its own CUDA graph (the C ABI is capturable: it only enqueues on the given
+    # stream); a step = five graph replays with an event between them, so the per-op device times come from INSIDE
+    # the timed region and the region is free of Python launch latency.  --eager times plain launches instead.
+    side = torch.cuda.Stream(device=dev)
+    op_fns = [
+        lambda: fn2.correlation(a, b, *CORR_ARGS, precision=precision),
+        lambda: fn2.correlation_grad(g, a, b, *CORR_ARGS, precision=precision),
+        lambda: fn2.flow_warp(image, flow),
+        lambda: fn2.flow_warp_grad(image, flow, gimg),
+        lambda: [fn2.downsample(gt, list(s)) for s in DS_SIZES],
+    ]
+    graphs, keep, launches_per_step = [], [], 0
+    if not args.eager:
+        with torch.cuda.stream(side):
+            for fn in op_fns:
+                fn()
+                torch.cuda.synchronize()
+                gr = torch.cuda.CUDAGraph()
+                l0 = _lib.launch_count()
+                with torch.cuda.graph(gr, stream=side):
+                    keep.append(fn())
+                launches_per_step += _lib.launch_count() - l0
+                graphs.append(gr)
+            for _ in range(warm):
+                for gr in graphs:
+                    gr.replay()
+        barrier()
+
     sampler = ClockSampler(local) if rank == 0 else None
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = _lib.launch_count()
     barrier()
     t0 = time.time()
-    start.record()
-    for k in range(args.steps):
-        step(evs[k])
-    stop.record()
+    if graphs:
+        with torch.cuda.stream(side):
+            for k in range(args.steps):
+                for i, gr in enumerate(graphs):
+                    evs[k][i].record()
+                    gr.replay()
+            evs[args.steps - 1][5].record()
+    else:
+        for k in range(args.steps):
+            step(evs[k])
     barrier()
     t1 = time.time()
-    launches = _lib.launch_count() - launches0
-    elapsed_ms = start.elapsed_time(stop)
+    launches = launches_per_step * args.steps if graphs else _lib.launch_count() - launches0
+    last = 5
+    elapsed_ms = evs[0][0].elapsed_time(evs[args.steps - 1][last])
     clocks = sampler.stop(t0, t1) if sampler else None
     if world > 1:
         t = torch.tensor([elapsed_ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms = float(t.item())
-    per_op_ms = {name: sum(evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(args.steps)) / args.steps
+
+    def op_end(k, i):   # the event that closes op i of step k
+        if i < 4 or not graphs:
+            return evs[k][i + 1]
+        return evs[k + 1][0] if k + 1 < args.steps else evs[k][5]
+    per_op_ms = {name: sum(evs[k][i].elapsed_time(op_end(k, i)) for k in range(args.steps)) / args.steps
                  for i, name in enumerate(ops)}
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region --------
+    # Every step uploads ALL of its inputs from pinned host memory and downloads ALL of its results.  Three streams
+    # (upload / compute / download) with double-buffered device inputs and host outputs let step k+1's upload run
+    # under step k's compute and download (PCIe is full duplex); nothing is skipped or reused between steps.
     e2e = None
     if not args.no_e2e:
         pinned = [x.pin_memory() for x in host]
         h2d = sum(x.numel() * 4 for x in pinned)
-        outs_host = None
-        e2e_steps = max(3, min(args.steps, 10))
+        e2e_steps = max(4, min(args.steps, 20))
+        s_up, s_dn = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        s_cp = torch.cuda.current_stream(dev)
+        dev_in = [[torch.empty_like(x, device=dev) for x in pinned] for _ in range(2)]
+        host_out = [None, None]
+        up_done = [torch.cuda.Event() for _ in range(2)]
+        cp_done = [torch.cuda.Event() for _ in range(2)]
+        dn_done = [torch.cuda.Event() for _ in range(2)]
+        live = [None, None]
 
-        def e2e_step():
-            nonlocal outs_host
-            da, db, dg, dimg, dflow, dgimg, dgt = [x.to(dev, non_blocking=True) for x in pinned]
+        def e2e_step(k):
+            sl = k & 1
+            with torch.cuda.stream(s_up):
+                s_up.wait_event(cp_done[sl])          # step k-2 has finished reading this input set
+                for d, h in zip(dev_in[sl], pinned):
+                    d.copy_(h, non_blocking=True)
+                up_done[sl].record(s_up)
+            s_cp.wait_event(up_done[sl])
+            s_cp.wait_event(dn_done[sl])              # step k-2's results have left the device
+            da, db, dg, dimg, dflow, dgimg, dgt = dev_in[sl]
             res = [fn2.correlation(da, db, *CORR_ARGS, precision=precision)]
             res += list(fn2.correlation_grad(dg, da, db, *CORR_ARGS, precision=precision))
             res.append(fn2.flow_warp(dimg, dflow))
             res += list(fn2.flow_warp_grad(dimg, dflow, dgimg))
             res += [fn2.downsample(dgt, list(s)) for s in DS_SIZES]
-            if outs_host is None:
-                outs_host = [torch.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
-            for h, r in zip(outs_host, res):
-                h.copy_(r, non_blocking=True)
-            return res
+            cp_done[sl].record(s_cp)
+            live[sl] = res                            # keep the device results alive until their download ran
+            if host_out[sl] is None:
+                host_out[sl] = [torch.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
+            with torch.cuda.stream(s_dn):
+                s_dn.wait_event(cp_done[sl])
+                for h, r in zip(host_out[sl], res):
+                    h.copy_(r, non_blocking=True)
+                    r.record_stream(s_dn)
+                dn_done[sl].record(s_dn)
 
-        for _ in range(2):
-            e2e_step()
+        for k in range(4):
+            e2e_step(k)
         barrier()
         s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s2.record()
-        for _ in range(e2e_steps):
-            e2e_step()
-        e2.record()
+        s2.record(s_cp)
+        s_up.wait_event(s2)
+        for k in range(e2e_steps):
+            e2e_step(k)
+        s_cp.wait_event(dn_done[0])
+        s_cp.wait_event(dn_done[1])
+        e2.record(s_cp)
         barrier()
         ms = s2.elapsed_time(e2)
         if world > 1:
             t = torch.tensor([ms], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             ms = float(t.item())
-        d2h = sum(h.numel() * 4 for h in outs_host)
+        d2h = sum(h.numel() * 4 for h in host_out[0])
         e2e = {"value": world * B * e2e_steps / (ms / 1e3), "unit": "pairs/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": ms / e2e_steps}
+               "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": ms / e2e_steps,
+               "how": "public Python API, pinned host inputs and outputs, upload/compute/download streams"}
+        del live, dev_in
 
     if rank != 0:
         if world > 1:

@@ -29,6 +29,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = G builders, then
 // epilogue.
+#include <type_traits>
 #include "fn2_tc.cuh"
 
 namespace fn2 {
@@ -51,7 +52,7 @@ struct BwdParams {
   CUtensorMap x[2][4];  // [mode][class]: mode 0 (da) streams b, mode 1 (db) streams a
   const float* grad;
   float* out[2];        // da, db
-  int N, H, W, C, D, s2, ncls, R, GW;
+  int N, H, W, C, s2, ncls;
   int Hc[2], Wc[2];
   int Hcb[2];           // class-space rows of b / db (>= Hc + boff with row halos)
   int bH;               // full-resolution rows of b / db
@@ -76,8 +77,11 @@ constexpr size_t bwd_smem_bytes() {
   return 1024 + (size_t)NST * (XSTAGE + GSTAGE) + sizeof(BwdBarriers<NST>);
 }
 
-template <int NST, int MINB>
-__global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
+template <int NST, int S2, int R>
+__global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
+  static_assert(NST == 4, "the G builders unroll the stage ring by four");
+  constexpr int GW = 2 * R + 1;
+  constexpr int D = GW * GW;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sX = smem;
@@ -100,7 +104,6 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
   const int Ha = P.Hc[cy];
   const int r0 = ty * TILE_R, x0 = tx * TILE_C;
   if (r0 >= Hout || x0 >= Wc) return;  // whole CTA leaves together, before any barrier exists
-  const int R = P.R;
   // output row ro meets source rows ro + shift - R .. ro + shift + R  (shift = +boff for da, -boff for db)
   const int shift = mode ? -P.boff : P.boff;
   const int t_first = max(0, r0 + shift - R);
@@ -186,44 +189,79 @@ __global__ void __launch_bounds__(NTHREADS, MINB) corr_tc_bwd_kernel(const __gri
     const int bw = warp - 2;
     const int q = bw >> 1;            // block = output row r0 + q of the tile
     const int xh = (bw & 1) * 16;     // this warp fills a-pixel rows xh .. xh+15 of the block
-    const int GW = P.GW;
     const int xb = lane;              // column of the block = b-pixel
-    for (int it = 0; it < nitems; ++it) {
-      const int stage = it % NST;
+    // Everything that does not change from item to item is hoisted: the swizzled shared-memory address of each of
+    // the thread's 16 elements, and (per 32-column source half hx) the validity mask of the 16 (a-pixel, b-pixel)
+    // pairs.  The 16 global addresses of an item are base + rr * (S2*D - 1) floats (next a-pixel, displacement
+    // one less), so they are immediates off one 64-bit base pointer.
+    constexpr int ESTRIDE = S2 * D - 1;
+    uint32_t saddr[16];
+    uint32_t okmask[2] = {0u, 0u};
+    const uint32_t sG_q = smem_u32(sG) + (uint32_t)q * GBLOCK;
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+      const int x = xh + rr;
+      // mode 0: K-major operand, SWIZZLE_128B (16-byte chunk ^ (row & 7)); mode 1: MN-major operand,
+      // SWIZZLE_128B_BASE32B (32-byte unit ^ (row & 3))
+      const int off = mode ? ((((xb >> 3) ^ (x & 3)) << 5) | ((xb & 7) << 2))
+                           : ((((xb >> 2) ^ (x & 7)) << 4) | ((xb & 3) << 2));
+      saddr[rr] = sG_q + (uint32_t)(x * 128 + off);
+#pragma unroll
+      for (int hx = 0; hx < 2; ++hx) {
+        const int xs0 = nhx > 1 ? x0 - 16 + 32 * hx : 0;
+        const int aabs = (mode ? xs0 : x0) + x, babs = (mode ? x0 : xs0) + xb;
+        const int o = babs - aabs + R;
+        const bool ok = (aabs >= 0) && (aabs < Wc) && (babs >= 0) && (babs < Wc) && (o >= 0) && (o < GW);
+        okmask[hx] |= (ok ? 1u : 0u) << rr;
+      }
+    }
+    const bool qrow_ok = (r0 + q < Hout);
+    const float* gimg = P.grad + (size_t)n * P.H * P.W * D;
+
+    // The gather of one item (16 floats per thread, 84-byte runs of `gradients`) is a full L2/DRAM round trip, so
+    // item it+1 is fetched into registers before item it is waited for and stored: two round trips in flight.
+    auto load_item = [&](int it, float (&v)[16]) {
       const int tt = t_first + it / nhx;
-      const int xs0 = nhx > 1 ? x0 - 16 + 32 * (it % nhx) : 0;
+      const int hx = it % nhx;
+      const int xs0 = nhx > 1 ? x0 - 16 + 32 * hx : 0;
       // a-row and displacement row of this block for this source row: b-row = a-row + boff + p
       const int ya = mode ? tt : r0 + q;
       const int p = mode ? (r0 + q - P.boff - tt) : (tt - P.boff - (r0 + q));
-      const bool blk_ok = (ya < Ha) && (r0 + q < Hout) && (p >= -R) && (p <= R);
+      const bool blk_ok = qrow_ok && (ya < Ha) && (p >= -R) && (p <= R);
+      const uint32_t m = blk_ok ? okmask[hx] : 0u;
       // block rows are a-pixels, block columns are b-pixels; the tile owns the a-columns for da, the b-columns for db
-      const int a0 = mode ? xs0 : x0, b0 = mode ? x0 : xs0;
-      const int babs = b0 + xb;
-      float v[16];
-      const float* grow = P.grad + (((size_t)n * P.H + (size_t)((blk_ok ? ya : 0) * P.s2 + cy)) * P.W + cx) * P.D +
-                          (p + R) * GW;
+      const int a0 = (mode ? xs0 : x0) + xh, b0 = (mode ? x0 : xs0) + xb;
+      const float* base = gimg + ((ptrdiff_t)((blk_ok ? ya : 0) * S2 + cy) * P.W + cx) * D + (blk_ok ? p + R : 0) * GW +
+                          (ptrdiff_t)a0 * (S2 * D) + (b0 - a0 + R);
 #pragma unroll
-      for (int rr = 0; rr < 16; ++rr) {
-        const int x = xh + rr;
-        const int aabs = a0 + x;
-        const int o = babs - aabs + R;
-        const bool ok = blk_ok && (aabs >= 0) && (aabs < Wc) && (babs >= 0) && (babs < Wc) && (o >= 0) && (o < GW);
-        v[rr] = ok ? __ldg(grow + (ptrdiff_t)aabs * P.s2 * P.D + o) : 0.f;
-      }
-      mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
-      uint8_t* blk = sG + (size_t)stage * GSTAGE + (size_t)q * GBLOCK;
+      for (int rr = 0; rr < 16; ++rr) v[rr] = ((m >> rr) & 1u) ? __ldg(base + rr * ESTRIDE) : 0.f;
+    };
+    {
+      float va[16], vb[16];
+      load_item(0, va);
+      for (int it0 = 0; it0 < nitems; it0 += NST) {
+        const uint32_t par = ((it0 / NST) & 1) ^ 1;
+        auto stage_body = [&](auto ST) {     // stage == ST: compile-time offsets into the G ring
+          constexpr int st = decltype(ST)::value;
+          const int it = it0 + st;
+          if (it < nitems) {
+            float (&cur)[16] = (st & 1) ? vb : va;
+            float (&nxt)[16] = (st & 1) ? va : vb;
+            if (it + 1 < nitems) load_item(it + 1, nxt);
+            mbar_wait(smem_u32(&bars->empty[st]), par);
 #pragma unroll
-      for (int rr = 0; rr < 16; ++rr) {
-        const int x = xh + rr;
-        // mode 0: K-major operand, SWIZZLE_128B (16-byte chunk ^ (row & 7)); mode 1: MN-major operand,
-        // SWIZZLE_128B_BASE32B (32-byte unit ^ (row & 3))
-        const int off = mode ? ((((xb >> 3) ^ (x & 3)) << 5) | ((xb & 7) << 2))
-                             : ((((xb >> 2) ^ (x & 7)) << 4) | ((xb & 3) << 2));
-        *reinterpret_cast<float*>(blk + x * 128 + off) = v[rr];
+            for (int rr = 0; rr < 16; ++rr)
+              asm volatile("st.shared.f32 [%0+%2], %1;" ::"r"(saddr[rr]), "f"(cur[rr]), "n"(st * GSTAGE) : "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&bars->g_full[st]));
+          }
+        };
+        stage_body(std::integral_constant<int, 0>{});
+        stage_body(std::integral_constant<int, 1>{});
+        stage_body(std::integral_constant<int, 2>{});
+        stage_body(std::integral_constant<int, 3>{});
       }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars->g_full[stage]));
     }
 
     // ---- epilogue: D^T[channel lane, output pixel column] -> out[pixel, channel] ----
@@ -267,6 +305,7 @@ bool corr_tc_bwd_supported(const CorrGeom& g, int precision) {
   if (g.s2 != 1 && g.s2 != 2) return false;
   if (g.C % KCH != 0 || g.C / KCH > MAX_CH) return false;
   if (g.bTop % g.s2 != 0) return false;
+  if (g.r != 10) return false;     // window radius instantiated below
   return true;
 }
 
@@ -276,8 +315,7 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
   BwdParams P;
   P.grad = gout;
   P.out[0] = ga; P.out[1] = gb;
-  P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
-  P.R = g.r; P.GW = g.gw;
+  P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
   P.bH = g.bH; P.boff = g.bTop / g.s2;
   for (int c = 0; c < 2; ++c) {
     P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
@@ -304,12 +342,16 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
         return FN2_E_CUDA;
     }
   }
-  auto kern = corr_tc_bwd_kernel<BWD_NST, 1>;
+  auto kern = g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST, 2, 10> : corr_tc_bwd_kernel<BWD_NST, 1, 10>;
   constexpr size_t smem = bwd_smem_bytes<BWD_NST>();
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    attr_err = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 2, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 1, 10>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX * 2;

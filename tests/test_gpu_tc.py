@@ -75,16 +75,21 @@ def test_tf32_full_size_properties():
     assert (out[:, 0, :, :10 * 21] == 0).all() and (out[:, :, 0].reshape(N, H, 21, 21)[..., :10] == 0).all()
     g = grad_like(out.shape).cuda()
     ga, gb = fn2.correlation_grad(g, a, b, *ARGS, precision="tf32")
-    assert torch.equal(fn2.correlation_grad(g[7:8].contiguous(), a[7:8].contiguous(), b[7:8].contiguous(), *ARGS,
-                                            precision="tf32")[0][0], ga[7])
-    da, db = torch.randn_like(a), torch.randn_like(b)
-    # <corr(da, b), g> == <ga, da> and <corr(a, db), g> == <gb, db> up to tf32 rounding of each side
+    ga7, gb7 = fn2.correlation_grad(g[7:8].contiguous(), a[7:8].contiguous(), b[7:8].contiguous(), *ARGS,
+                                    precision="tf32")
+    assert torch.equal(ga7[0], ga[7]) and torch.equal(gb7[0], gb[7])
+    gen = torch.Generator(device="cuda").manual_seed(99)
+    da = torch.randn(a.shape, device="cuda", generator=gen)
+    db = torch.randn(b.shape, device="cuda", generator=gen)
+    # <corr(da, b), g> == <ga, da> and <corr(a, db), g> == <gb, db>.  Both sides round every product to tf32 (and the
+    # tensor core truncates), and the totals are cancellation-heavy sums, so the bound is relative to the sum of
+    # magnitudes: 2^-10 per operand pair would allow 2e-3; 5e-4 is what independent rounding leaves.
     lhs = (fn2.correlation(da, b, *ARGS, precision="tf32").double() * g.double()).sum()
-    rhs = (ga.double() * da.double()).sum()
-    assert abs(lhs - rhs) <= 2e-3 * abs(rhs) + 1e-2
+    prod = ga.double() * da.double()
+    assert abs(lhs - prod.sum()) <= 5e-4 * prod.abs().sum()
     lhs = (fn2.correlation(a, db, *ARGS, precision="tf32").double() * g.double()).sum()
-    rhs = (gb.double() * db.double()).sum()
-    assert abs(lhs - rhs) <= 2e-3 * abs(rhs) + 1e-2
+    prod = gb.double() * db.double()
+    assert abs(lhs - prod.sum()) <= 5e-4 * prod.abs().sum()
 
 
 def test_unsupported_precision_is_an_error_not_a_fallback():
