@@ -7,18 +7,18 @@
 // is the banded "gradient Gram matrix".  Both gradients are dense GEMMs against G, so no scatter and no atomics:
 // every output element is produced by exactly one CTA.
 //
-// One CTA owns a tile of 4 class-rows x 32 class-cols of OUTPUT pixels (a-pixels for da: mode 0, b-pixels for db:
-// mode 1) and all C channels, and walks over the <= 4+2r source rows t of the other tensor X (b for da, a for db):
-//   D^T[c, out pixel] += X_t^T[c, src pixel] * Gblk_t[src pixel, out pixel]       (M = 128 channels, N = 128, K = 32)
+// One CTA owns a tile of 8 class-rows x 32 class-cols of OUTPUT pixels (a-pixels for da: mode 0, b-pixels for db:
+// mode 1) and all C channels, and walks over the <= 8+2r source rows t of the other tensor X (b for da, a for db):
+//   D^T[c, out pixel] += X_t^T[c, src pixel] * Gblk_t[src pixel, out pixel]       (M = 128 channels, N = 256, K = 32)
 //   * X_t (32 pixels x C channels, NHWC) arrives by TMA as C/32 chunks of [32 pixels][32 channels] (swizzle
 //     128B_ATOM_32B, the one layout the tensor core accepts for an MN-major 32-bit operand); read as the MN-major A
 //     operand (channels contiguous) -- no transpose, no conversion: fp32 bits are consumed as tf32.
-//   * Gblk_t is built by eight warps straight from `gradients` into shared memory in the same swizzled layout: four
+//   * Gblk_t is built by sixteen warps straight from `gradients` into shared memory in the same swizzled layout: eight
 //     32x32 blocks (one per output row of the tile), rows = a-pixel, cols = b-pixel, each row the 21-float run
 //     grad[i, p, :] shifted to its diagonal position.  The same bytes are a K-major B operand for da (N = a-pixel
 //     rows, K = b-pixel cols) and an MN-major B operand for db (N = b-pixel cols, K = a-pixel rows).
-//   * the accumulator D^T (2 halves of 128 channels x 128 output pixels, fp32) lives in 256 TMEM columns; after the
-//     last source row the same eight warps read it back (lane = channel) and store 128-byte channel runs.
+//   * the accumulator D^T (2 halves of 128 channels x 256 output pixels, fp32) fills the 512 TMEM columns; after the
+//     last source row the same sixteen warps read it back (lane = channel) and store 128-byte channel runs.
 // CTAs of the two modes for the same image are adjacent in the grid so the second read of `gradients` hits L2.
 //
 // Wide images (class width > 32): output tiles are 32 columns wide and need source columns x0-10 .. x0+41, so each
@@ -27,7 +27,7 @@
 // y + boff + p in class space.  db is produced for every row of the tall tensor (halo rows = the partial sums the
 // neighbouring strip adds to its own).
 //
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = G builders, then
+// Warp roles (576 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-17 = G builders, then
 // epilogue.
 #include <type_traits>
 #include "fn2_tc.cuh"
@@ -37,16 +37,17 @@ namespace {
 
 using namespace tc;
 
-constexpr int TILE_R = 4;                 // output rows per tile (class space)
+constexpr int TILE_R = 8;                 // output rows per tile (class space)
 constexpr int TILE_C = 32;                // output cols per tile
 constexpr int XCHUNK = 32 * 128;          // one X chunk: 32 pixels x 32 channels fp32 = 4 KB
 constexpr int MAX_CH = 8;                 // C <= 256
 constexpr int XSTAGE = MAX_CH * XCHUNK;   // 32 KB per stage
 constexpr int GBLOCK = 32 * 128;          // one G block: 32 a-pixels x 32 b-pixels fp32 = 4 KB
-constexpr int GSTAGE = TILE_R * GBLOCK;   // 16 KB per stage
-constexpr int NBUILD = 8;                 // builder / epilogue warps
+constexpr int GSTAGE = TILE_R * GBLOCK;   // 32 KB per stage
+constexpr int NBUILD = 2 * TILE_R;        // builder / epilogue warps: two per output row of the tile
 constexpr int NTHREADS = 64 + 32 * NBUILD;
-constexpr int TMEM_COLS = 256;
+constexpr int TILE_N = TILE_R * TILE_C;    // output pixels per tile = N of the MMA (256)
+constexpr int TMEM_COLS = 2 * TILE_N;      // two 128-channel halves of the accumulator
 
 struct BwdParams {
   CUtensorMap x[2][4];  // [mode][class]: mode 0 (da) streams b, mode 1 (db) streams a
@@ -79,7 +80,7 @@ constexpr size_t bwd_smem_bytes() {
 
 template <int NST, int S2, int R>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
-  static_assert(NST == 4, "the G builders unroll the stage ring by four");
+  static_assert(NST == 3 || NST == 4, "the G builders unroll the stage ring explicitly");
   constexpr int GW = 2 * R + 1;
   constexpr int D = GW * GW;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -162,7 +163,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
       // A = X^T: MN-major (channels contiguous), M = 128 channels = 4 chunks (LBO = chunk stride), K = 8 pixel rows.
       // B = G  : mode 0 K-major (N = a-pixel rows, K = b-pixel cols); mode 1 MN-major (N = b-pixel cols, LBO = block
       //          stride, K = a-pixel rows).
-      const uint32_t idesc = idesc_tf32_major(128, 128, 1, mode);
+      const uint32_t idesc = idesc_tf32_major(128, TILE_N, 1, mode);
       for (int it = 0; it < nitems; ++it) {
         const int stage = it % NST;
         const uint32_t par = (it / NST) & 1;
@@ -177,7 +178,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
             const uint64_t adesc = desc_sw128b32_mnmajor(x_addr + h * 4 * XCHUNK + k8 * 1024, XCHUNK, 512);
             const uint64_t bdesc = mode ? desc_sw128b32_mnmajor(g_addr + k8 * 1024, GBLOCK, 512)
                                         : desc_sw128_kmajor(g_addr + k8 * 32);
-            umma_tf32(tmem_base + (uint32_t)h * 128, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
+            umma_tf32(tmem_base + (uint32_t)h * TILE_N, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
           }
         }
         umma_commit(smem_u32(&bars->empty[stage]));  // frees X and G of this stage once the MMAs have read them
@@ -219,7 +220,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     const float* gimg = P.grad + (size_t)n * P.H * P.W * D;
 
     // The gather of one item (16 floats per thread, 84-byte runs of `gradients`) is a full L2/DRAM round trip, so
-    // item it+1 is fetched into registers before item it is waited for and stored: two round trips in flight.
+    // items it+1 .. it+NST-1 are fetched into registers before item it is waited for and stored.
     auto load_item = [&](int it, float (&v)[16]) {
       const int tt = t_first + it / nhx;
       const int hx = it % nhx;
@@ -237,17 +238,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
       for (int rr = 0; rr < 16; ++rr) v[rr] = ((m >> rr) & 1u) ? __ldg(base + rr * ESTRIDE) : 0.f;
     };
     {
-      float va[16], vb[16];
-      load_item(0, va);
+      float vq[NST][16];   // register ring aligned with the stage ring: item it lives in vq[it % NST]
+      load_item(0, vq[0]);
+#pragma unroll
+      for (int i = 1; i < NST - 1; ++i)
+        if (i < nitems) load_item(i, vq[i]);
       for (int it0 = 0; it0 < nitems; it0 += NST) {
         const uint32_t par = ((it0 / NST) & 1) ^ 1;
         auto stage_body = [&](auto ST) {     // stage == ST: compile-time offsets into the G ring
           constexpr int st = decltype(ST)::value;
           const int it = it0 + st;
           if (it < nitems) {
-            float (&cur)[16] = (st & 1) ? vb : va;
-            float (&nxt)[16] = (st & 1) ? va : vb;
-            if (it + 1 < nitems) load_item(it + 1, nxt);
+            float (&cur)[16] = vq[st];
+            if (it + NST - 1 < nitems) load_item(it + NST - 1, vq[(st + NST - 1) % NST]);
             mbar_wait(smem_u32(&bars->empty[st]), par);
 #pragma unroll
             for (int rr = 0; rr < 16; ++rr)
@@ -260,7 +263,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
         stage_body(std::integral_constant<int, 0>{});
         stage_body(std::integral_constant<int, 1>{});
         stage_body(std::integral_constant<int, 2>{});
-        stage_body(std::integral_constant<int, 3>{});
+        if constexpr (NST == 4) stage_body(std::integral_constant<int, 3>{});
       }
     }
 
@@ -268,15 +271,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     mbar_wait(smem_u32(&bars->acc_full), 0);
     tc_fence_after();
     const int qd = warp & 3;        // TMEM lane quadrant this warp may read
-    const int e = bw >> 2;          // the two warps of a quadrant take alternate output rows
+    const int e = bw >> 2;          // the NBUILD/4 warps of a quadrant take alternate output rows
     const float inv = P.inv;
     for (int h = 0; h < P.nhalf; ++h) {
       const int ch = h * 128 + qd * 32 + lane;
-      for (int qq = e; qq < TILE_R; qq += 2) {
+      for (int qq = e; qq < TILE_R; qq += NBUILD / 4) {
         const int row = r0 + qq;
         if (row >= Hout) continue;  // warp-uniform
         float v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * 128 + qq * 32), v);
+        tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * TILE_N + qq * 32), v);
         float* orow = outp + (((size_t)n * Hfull + (size_t)(row * P.s2 + cy)) * P.W + cx + (size_t)x0 * P.s2) * P.C + ch;
         if (ch < P.C) {
 #pragma unroll
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
   }
 }
 
-constexpr int BWD_NST = 4;
+constexpr int BWD_NST = 3;
 
 }  // namespace
 
