@@ -397,6 +397,7 @@ int flow_warp_forward(const float* image, const float* flow, float* out, int N, 
                       cudaStream_t st) {
   const long long npix = (long long)N * H * W;
   if ((npix + WARP_PIX - 1) / WARP_PIX > 0x7fffffffLL || (npix + 7) / 8 > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  if (flow_warp_tile_supported(H, W, C)) return flow_warp_tile_forward(image, flow, out, N, H, W, C, st);
   switch (C) {
     case 1: return launch_fwd_narrow<1>(image, flow, out, npix, H, W, st);
     case 2: return launch_fwd_narrow<2>(image, flow, out, npix, H, W, st);
@@ -418,6 +419,7 @@ int flow_warp_backward(const float* image, const float* flow, const float* gout,
   if ((npix + WARP_PIX - 1) / WARP_PIX > 0x7fffffffLL || (npix + 7) / 8 > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   cudaError_t e = cudaMemsetAsync(gimage, 0, sizeof(float) * (size_t)npix * C, st);
   if (e != cudaSuccess) { note_cuda_error(e); return FN2_E_CUDA; }
+  if (flow_warp_tile_supported(H, W, C)) return flow_warp_tile_backward(image, flow, gout, gimage, gflow, N, H, W, C, st);
   switch (C) {
     case 1: return launch_bwd_narrow<1>(image, flow, gout, gimage, gflow, npix, H, W, st);
     case 2: return launch_bwd_narrow<2>(image, flow, gout, gimage, gflow, npix, H, W, st);

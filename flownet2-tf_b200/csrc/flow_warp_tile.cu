@@ -1,0 +1,356 @@
+// flow_warp_tile.cu -- flow_warp forward / backward for narrow images (C <= 4) with the sampled neighbourhood staged
+// in shared memory.  Semantics: flow_warp.cu.cc:42-94, flow_warp_grad.cu.cc:30-87.
+//
+// A per-pixel gather straight from global memory is bound by L1 wavefronts: with flows of a few pixels every lane of
+// a warp touches its own pair of 32-byte sectors in two image rows.  But the taps of a TILE of output pixels all fall
+// in the tile grown by the flow magnitude.  One CTA owns a 32 x 64 tile of output pixels, has the TMA unit copy the
+// window [tile - margin, tile + margin] of the image into shared memory (cp.async.bulk.tensor: no LSU instructions,
+// parts of the window outside the image are zero fill; each image byte is fetched from L2 once per neighbouring tile
+// instead of once per tap), and the four taps become shared-memory reads.  A pixel whose taps leave the window (flow larger than the margin) takes them from global memory instead:
+// any flow is handled, only the common case is fast.
+//
+// Backward, image gradient: the same window, zero-initialised, collects the four-tap scatter with shared-memory
+// adds; it is then flushed row by row with bulk reduce-adds (cp.reduce.async.bulk .add.f32) instead of 12 scattered
+// atomics per pixel.  Out-of-window taps go to global atomics directly.
+// Backward, flow gradient: a gather like the forward, from the staged image window.
+#include <cstdlib>
+#include <mutex>
+#include "fn2_tc.cuh"
+
+namespace fn2 {
+namespace {
+
+constexpr int TH = 32, TW = 64;        // output tile
+constexpr int NT = 512;                // threads per CTA: 4 consecutive pixels each
+constexpr int PXT = 4;
+
+using namespace tc;
+
+template <int C>
+struct Win {
+  // margins sized so the window fits ~110 KB (two CTAs per SM): C <= 3 -> 77 x 120 pixels, C == 4 -> 65 x 104
+  static constexpr int MY = (C <= 3) ? 22 : 16;
+  static constexpr int MX = (C <= 3) ? 24 : 16;
+  static constexpr int ROWS = TH + 2 * MY + 1;
+  static constexpr int COLS = (C <= 3) ? 120 : 104;                  // >= TW + 2*MX + 1
+  static constexpr int NB = (COLS * C + 255) / 256;                  // TMA boxes (inner box dimension <= 256 elements)
+  static constexpr int PXB = COLS / NB;                              // pixels per box
+  static constexpr int BW = PXB * C;                                 // floats per box row
+  static constexpr int BOX_FLOATS = ((ROWS * BW * 4 + 127) / 128) * 32;   // box size rounded up to 128 bytes
+  static constexpr uint32_t TX_BYTES = (uint32_t)NB * ROWS * BW * 4;
+  static constexpr size_t BYTES = (size_t)NB * BOX_FLOATS * sizeof(float) + 128;
+  static_assert(COLS % NB == 0 && (BW * 4) % 16 == 0 && COLS >= TW + 2 * MX + 1, "window geometry");
+  // float offset of pixel column px (0 <= px < COLS) of window row r
+  __device__ static __forceinline__ int at(int r, int px) {
+    const int box = (NB > 1 && px >= PXB) ? 1 : 0;
+    return box * BOX_FLOATS + r * BW + (px - box * PXB) * C;
+  }
+};
+
+struct Tile {
+  int n, ty0, tx0;          // image, tile origin
+  int wy0, wx0;             // window origin (may be negative: zero fill)
+};
+
+template <int C>
+__device__ __forceinline__ Tile make_tile(int tilesX, int tilesY) {
+  Tile t;
+  int b = blockIdx.x;
+  const int txi = b % tilesX; b /= tilesX;
+  const int tyi = b % tilesY;
+  t.n = b / tilesY;
+  t.ty0 = tyi * TH; t.tx0 = txi * TW;
+  t.wy0 = t.ty0 - Win<C>::MY;
+  t.wx0 = t.tx0 - Win<C>::MX;
+  return t;
+}
+
+__device__ __forceinline__ float* align128(float* p) {
+  return p + (((128u - (smem_u32(p) & 127u)) & 127u) >> 2);
+}
+
+struct Taps {
+  bool in;
+  int L, T, R, B;
+  float alpha, beta, x2, y2;
+};
+
+__device__ __forceinline__ Taps make_taps(float fx, float fy, int x, int y, int W, int H) {
+  Taps t;
+  const float x2 = float(x) + fx, y2 = float(y) + fy;
+  t.x2 = x2; t.y2 = y2;
+  t.in = (x2 >= 0.f) && (y2 >= 0.f) && (x2 < float(W)) && (y2 < float(H));   // NaN -> false (flow_warp.cu.cc:74)
+  t.L = t.in ? int(x2) : 0;
+  t.T = t.in ? int(y2) : 0;
+  t.R = min(t.L + 1, W - 1);
+  t.B = min(t.T + 1, H - 1);
+  t.alpha = x2 - float(t.L);
+  t.beta = y2 - float(t.T);
+  return t;
+}
+
+// ------------------------------------------------------------------------------------------------ forward
+// MODE 0: out = warp(image, flow).   MODE 1: flow gradient (needs gout), same gather.
+template <int C, int MODE>
+__global__ void __launch_bounds__(NT, 2) warp_tile_gather(const __grid_constant__ CUtensorMap imap,
+                                                          const float* __restrict__ image,
+                                                          const float* __restrict__ flow,
+                                                          const float* __restrict__ gout, float* __restrict__ out,
+                                                          int H, int W, int tilesX, int tilesY) {
+  extern __shared__ __align__(128) float win_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  float* win = align128(win_raw);
+  const Tile t = make_tile<C>(tilesX, tilesY);
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_expect_tx(smem_u32(&bar), Win<C>::TX_BYTES);
+#pragma unroll
+    for (int b = 0; b < Win<C>::NB; ++b)
+      tma_load_3d(smem_u32(win + b * Win<C>::BOX_FLOATS), &imap, smem_u32(&bar), t.wx0 * C + b * Win<C>::BW, t.wy0,
+                  t.n);
+  }
+  __syncthreads();   // the barrier is initialised before anyone polls it
+  const int y = t.ty0 + threadIdx.x / (TW / PXT);
+  const int x = t.tx0 + (threadIdx.x % (TW / PXT)) * PXT;
+  const bool live = (y < H) && (x < W);          // W % 4 == 0: a group of 4 pixels is inside or outside as a whole
+  const size_t pix = ((size_t)t.n * H + (live ? y : 0)) * W + (live ? x : 0);
+
+  float2 f[PXT];
+  float g[PXT][C];
+  if (live) {   // issued before the window copy so the latencies overlap
+    const float4 f01 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2));
+    const float4 f23 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2) + 1);
+    f[0] = make_float2(f01.x, f01.y); f[1] = make_float2(f01.z, f01.w);
+    f[2] = make_float2(f23.x, f23.y); f[3] = make_float2(f23.z, f23.w);
+    if (MODE == 1) {
+      float gv[PXT * C];
+#pragma unroll
+      for (int v = 0; v < C; ++v) {
+        const float4 q = __ldg(reinterpret_cast<const float4*>(gout + pix * C) + v);
+        gv[4 * v] = q.x; gv[4 * v + 1] = q.y; gv[4 * v + 2] = q.z; gv[4 * v + 3] = q.w;
+      }
+#pragma unroll
+      for (int i = 0; i < PXT; ++i)
+#pragma unroll
+        for (int c = 0; c < C; ++c) g[i][c] = gv[i * C + c];
+    }
+  }
+  mbar_wait(smem_u32(&bar), 0);
+  if (!live) return;
+
+  float res[PXT * C];     // MODE 0: warped pixels
+  float2 gf[PXT];         // MODE 1: flow gradients
+  const float* img = image + (size_t)t.n * H * W * C;
+#pragma unroll
+  for (int i = 0; i < PXT; ++i) {
+    const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
+    float iTL[C], iTR[C], iBL[C], iBR[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) iTL[c] = iTR[c] = iBL[c] = iBR[c] = 0.f;
+    if (tp.in) {
+      const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
+                         (tp.R < t.wx0 + Win<C>::COLS);
+      if (inwin) {
+        const float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
+        const float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
+        const int dB = (tp.B - tp.T) * Win<C>::BW;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          iTL[c] = pL[c]; iTR[c] = pR[c]; iBL[c] = pL[dB + c]; iBR[c] = pR[dB + c];
+        }
+      } else {
+        const float* pT = img + ((size_t)tp.T * W + tp.L) * C;
+        const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          iTL[c] = __ldg(pT + c); iTR[c] = __ldg(pT + dR + c);
+          iBL[c] = __ldg(pT + dB + c); iBR[c] = __ldg(pT + dB + dR + c);
+        }
+      }
+    }
+    if (MODE == 0) {
+      const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
+      const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
+#pragma unroll
+      for (int c = 0; c < C; ++c)
+        res[i * C + c] = tp.in ? cTL * iTL[c] + cTR * iTR[c] + cBL * iBL[c] + cBR * iBR[c] : 0.f;
+    } else {
+      const float gy = float(tp.B) - tp.y2;  // flow_warp_grad.cu.cc:55
+      const float gx = float(tp.R) - tp.x2;  // :72
+      float bx = 0.f, by = 0.f;
+#pragma unroll
+      for (int c = 0; c < C; ++c) {
+        float tx = gy * (iTR[c] - iTL[c]);
+        tx += (1 - gy) * (iBR[c] - iBL[c]);
+        bx += g[i][c] * tx;
+        float ty = gx * (iBL[c] - iTL[c]);
+        ty += (1 - gx) * (iBR[c] - iTR[c]);
+        by += g[i][c] * ty;
+      }
+      gf[i] = tp.in ? make_float2(bx, by) : make_float2(0.f, 0.f);
+    }
+  }
+  if (MODE == 0) {
+#pragma unroll
+    for (int v = 0; v < C; ++v)
+      reinterpret_cast<float4*>(out + pix * C)[v] = make_float4(res[4 * v], res[4 * v + 1], res[4 * v + 2], res[4 * v + 3]);
+  } else {
+    reinterpret_cast<float4*>(out + pix * 2)[0] = make_float4(gf[0].x, gf[0].y, gf[1].x, gf[1].y);
+    reinterpret_cast<float4*>(out + pix * 2)[1] = make_float4(gf[2].x, gf[2].y, gf[3].x, gf[3].y);
+  }
+}
+
+// ------------------------------------------------------------------------------------- backward: image gradient
+template <int C>
+__global__ void __launch_bounds__(NT, 2) warp_tile_scatter(const float* __restrict__ flow,
+                                                           const float* __restrict__ gout,
+                                                           float* __restrict__ gimage, int H, int W, int tilesX,
+                                                           int tilesY) {
+  extern __shared__ __align__(128) float win_raw[];
+  float* win = align128(win_raw);
+  const Tile t = make_tile<C>(tilesX, tilesY);
+  const int y = t.ty0 + threadIdx.x / (TW / PXT);
+  const int x = t.tx0 + (threadIdx.x % (TW / PXT)) * PXT;
+  const bool live = (y < H) && (x < W);
+  const size_t pix = ((size_t)t.n * H + (live ? y : 0)) * W + (live ? x : 0);
+
+  float2 f[PXT];
+  float gv[PXT * C];
+  if (live) {
+    const float4 f01 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2));
+    const float4 f23 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2) + 1);
+    f[0] = make_float2(f01.x, f01.y); f[1] = make_float2(f01.z, f01.w);
+    f[2] = make_float2(f23.x, f23.y); f[3] = make_float2(f23.z, f23.w);
+#pragma unroll
+    for (int v = 0; v < C; ++v) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(gout + pix * C) + v);
+      gv[4 * v] = q.x; gv[4 * v + 1] = q.y; gv[4 * v + 2] = q.z; gv[4 * v + 3] = q.w;
+    }
+  }
+  for (int i = threadIdx.x; i < Win<C>::NB * Win<C>::BOX_FLOATS / 4; i += NT)
+    reinterpret_cast<float4*>(win)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+
+  if (live) {
+    float* gimg = gimage + (size_t)t.n * H * W * C;
+#pragma unroll
+    for (int i = 0; i < PXT; ++i) {
+      const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
+      if (!tp.in) continue;
+      const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
+      const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
+      const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
+                         (tp.R < t.wx0 + Win<C>::COLS);
+      if (inwin) {
+        float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
+        float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
+        const int dB = (tp.B - tp.T) * Win<C>::BW;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float gc = gv[i * C + c];
+          atomicAdd(pL + c, gc * cTL);
+          atomicAdd(pR + c, gc * cTR);
+          atomicAdd(pL + dB + c, gc * cBL);
+          atomicAdd(pR + dB + c, gc * cBR);
+        }
+      } else {
+        float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;
+        const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float gc = gv[i * C + c];
+          atomicAdd(pT + c, gc * cTL);
+          atomicAdd(pT + dR + c, gc * cTR);
+          atomicAdd(pT + dB + c, gc * cBL);
+          atomicAdd(pT + dB + dR + c, gc * cBR);
+        }
+      }
+    }
+  }
+
+  // flush: every window row inside the image is one bulk reduce-add (cp.reduce.async.bulk .add.f32, executed by the
+  // copy engine: no LSU instructions), clipped to the image; offsets and sizes stay multiples of 16 bytes because
+  // W*C, MX*C and the box width are multiples of 4 floats.
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the async proxy
+  __syncthreads();
+  if (threadIdx.x < Win<C>::NB * Win<C>::ROWS) {
+    const int b = threadIdx.x / Win<C>::ROWS, r = threadIdx.x - b * Win<C>::ROWS;
+    const int yy = t.wy0 + r;
+    const int fc0 = t.wx0 * C + b * Win<C>::BW;
+    const int lo = max(fc0, 0), hi = min(fc0 + Win<C>::BW, W * C);
+    if (yy >= 0 && yy < H && hi > lo) {
+      float* dst = gimage + ((size_t)t.n * H + yy) * W * C + lo;
+      const uint32_t src = smem_u32(win + b * Win<C>::BOX_FLOATS + r * Win<C>::BW + (lo - fc0));
+      asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                   ::"l"(dst), "r"(src), "r"((uint32_t)(hi - lo) * 4u) : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory stays valid until it was read
+  }
+}
+
+template <int C>
+int launch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, int N, int H, int W,
+                cudaStream_t st) {
+  static std::once_flag once;
+  static cudaError_t err = cudaSuccess;
+  std::call_once(once, [] {
+    const int bytes = (int)Win<C>::BYTES;
+    err = cudaFuncSetAttribute(warp_tile_gather<C, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (err == cudaSuccess)
+      err = cudaFuncSetAttribute(warp_tile_gather<C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (err == cudaSuccess)
+      err = cudaFuncSetAttribute(warp_tile_scatter<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  });
+  if (err != cudaSuccess) { note_cuda_error(err); return FN2_E_CUDA; }
+  const int tilesX = (W + TW - 1) / TW, tilesY = (H + TH - 1) / TH;
+  const long long blocks = (long long)N * tilesX * tilesY;
+  if (blocks > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  const size_t smem = Win<C>::BYTES;
+  CUtensorMap map;   // over `image`, for the gathers
+  if (mode != 2 && !make_row_map(&map, image, N, H, W, C, Win<C>::BW, Win<C>::ROWS)) return FN2_E_CUDA;
+  if (mode == 0)
+    warp_tile_gather<C, 0><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, nullptr, out, H, W, tilesX, tilesY);
+  else if (mode == 1)
+    warp_tile_gather<C, 1><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, H, W, tilesX, tilesY);
+  else
+    warp_tile_scatter<C><<<(unsigned)blocks, NT, smem, st>>>(flow, gout, out, H, W, tilesX, tilesY);
+  return after_launch();
+}
+
+int dispatch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, int N, int H, int W,
+                  int C, cudaStream_t st) {
+  switch (C) {
+    case 1: return launch_tile<1>(mode, image, flow, gout, out, N, H, W, st);
+    case 2: return launch_tile<2>(mode, image, flow, gout, out, N, H, W, st);
+    case 3: return launch_tile<3>(mode, image, flow, gout, out, N, H, W, st);
+    case 4: return launch_tile<4>(mode, image, flow, gout, out, N, H, W, st);
+    default: return FN2_E_BAD_SHAPE;
+  }
+}
+
+}  // namespace
+
+bool flow_warp_tile_supported(int H, int W, int C) { return C >= 1 && C <= 4 && (W % 4) == 0 && H >= 1; }
+
+int flow_warp_tile_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
+                           cudaStream_t st) {
+  return dispatch_tile(0, image, flow, nullptr, out, N, H, W, C, st);
+}
+
+// gimage must already be zero (flow_warp_backward memsets it on the same stream)
+int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
+                            int N, int H, int W, int C, cudaStream_t st) {
+  const char* dbg = getenv("FN2_WARP_BWD_PART");   // developer switch: "1" flow gradient only, "2" image gradient only
+  const int part = dbg ? atoi(dbg) : 0;
+  if (part != 2) {
+    const int rc = dispatch_tile(1, image, flow, gout, gflow, N, H, W, C, st);
+    if (rc != FN2_OK) return rc;
+  }
+  if (part == 1) return FN2_OK;
+  return dispatch_tile(2, nullptr, flow, gout, gimage, N, H, W, C, st);
+}
+
+}  // namespace fn2

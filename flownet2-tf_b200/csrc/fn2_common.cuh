@@ -53,6 +53,12 @@ int flow_warp_forward(const float* image, const float* flow, float* out, int N, 
                       cudaStream_t st);
 int flow_warp_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow, int N,
                        int H, int W, int C, cudaStream_t st);
+// flow_warp_tile.cu: shared-memory window kernels for C <= 4, W % 4 == 0
+bool flow_warp_tile_supported(int H, int W, int C);
+int flow_warp_tile_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
+                           cudaStream_t st);
+int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
+                            int N, int H, int W, int C, cudaStream_t st);
 int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C, int oH, int oW, cudaStream_t st);
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

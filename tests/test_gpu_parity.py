@@ -98,7 +98,11 @@ def test_correlation_errors_on_device():
 
 
 @pytest.mark.parametrize("shape", [(2, 13, 17, 3), (1, 31, 33, 1), (1, 9, 40, 2), (2, 8, 8, 4), (1, 7, 9, 5),
-                                   (1, 6, 6, 64), (8, 384, 512, 3)])
+                                   (1, 6, 6, 64), (8, 384, 512, 3),
+                                   # W % 4 == 0 and C <= 4: the shared-memory window kernels (flow_warp_tile.cu);
+                                   # several tiles, ragged tile edges, windows clipped at every image border
+                                   (2, 40, 64, 3), (1, 70, 132, 3), (1, 33, 8, 1), (2, 37, 72, 2), (1, 64, 128, 4),
+                                   (1, 100, 200, 3)])
 def test_flow_warp_matches_oracle(shape):
     N, H, W, C = shape
     image, flow = warp_inputs(N, H, W, C)
