@@ -13,7 +13,6 @@
 // adds; it is then flushed row by row with bulk reduce-adds (cp.reduce.async.bulk .add.f32) instead of 12 scattered
 // atomics per pixel.  Out-of-window taps go to global atomics directly.
 // Backward, flow gradient: a gather like the forward, from the staged image window.
-#include <cstdlib>
 #include <mutex>
 #include "fn2_tc.cuh"
 
@@ -343,13 +342,8 @@ int flow_warp_tile_forward(const float* image, const float* flow, float* out, in
 // gimage must already be zero (flow_warp_backward memsets it on the same stream)
 int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
                             int N, int H, int W, int C, cudaStream_t st) {
-  const char* dbg = getenv("FN2_WARP_BWD_PART");   // developer switch: "1" flow gradient only, "2" image gradient only
-  const int part = dbg ? atoi(dbg) : 0;
-  if (part != 2) {
-    const int rc = dispatch_tile(1, image, flow, gout, gflow, N, H, W, C, st);
-    if (rc != FN2_OK) return rc;
-  }
-  if (part == 1) return FN2_OK;
+  const int rc = dispatch_tile(1, image, flow, gout, gflow, N, H, W, C, st);
+  if (rc != FN2_OK) return rc;
   return dispatch_tile(2, nullptr, flow, gout, gimage, N, H, W, C, st);
 }
 
