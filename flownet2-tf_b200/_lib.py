@@ -36,6 +36,8 @@ _SIGNATURES = {
     "fn2_flow_warp_forward": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
     "fn2_flow_warp_backward": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "fn2_downsample_forward": (c_int, [c_void_p] * 2 + [c_int] * 6 + [c_void_p]),
+    "fn2_downsample_multi_forward": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)] + [c_int] * 5
+                                     + [c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

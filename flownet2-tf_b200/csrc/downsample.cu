@@ -21,6 +21,7 @@
 #include <cooperative_groups.h>
 #include <mutex>
 #include "fn2_common.cuh"
+#include "fn2_downsample.cuh"
 
 namespace fn2 {
 namespace {
@@ -36,7 +37,6 @@ struct DsParams {
   int wr, hr;
 };
 
-__device__ __forceinline__ float nan_f() { return __int_as_float(0x7fffffff); }
 
 // G threads per output pixel, G in {8, 32, 256}; CTA = 256 threads.  C <= MAXC channels handled per lane.
 template <int G, int CT>
@@ -157,22 +157,6 @@ __global__ void __launch_bounds__(256) downsample_wide_kernel(DsParams p, const 
 // its two x-weights, to shared memory, and the (dx, sum) pairs are then added up by sub-warp groups in a fixed order.
 // Cluster ranks combine their partial rows through distributed shared memory.  Every input byte is read once from
 // DRAM (the (G+1)/G re-read of shared band rows hits L2), and the per-tap work is 3 FMAs per channel and live row.
-__device__ __forceinline__ float src_pos(int d, int on1, int in1) {
-  // downsample_kernel_gpu.cu.cc:40-41, this evaluation order; __fmul_rn keeps the product a rounded fp32 value (the
-  // compiler would otherwise fuse it into the subtraction of tri() and shift every weight by up to 4e-6)
-  return __fmul_rn(__fdiv_rn((float)d, (float)on1), (float)in1);
-}
-__device__ __forceinline__ float tri(float off, float src, float scale) {
-  return fmaxf(0.0f, 1.0f - (fabsf(off - src) / scale));   // :59-60
-}
-// last output index d in [0, on) whose centre is <= pos (centres are increasing); 0 if none
-__device__ __forceinline__ int last_centre_le(int pos, float scale, int on, int in_) {
-  int d = min(on - 1, max(0, (int)((float)pos / scale)));
-  while (d + 1 < on && src_pos(d + 1, on - 1, in_ - 1) <= (float)pos) ++d;
-  while (d > 0 && src_pos(d, on - 1, in_ - 1) > (float)pos) --d;
-  return d;
-}
-
 struct BandPlan {
   int G, rs, px;
 };

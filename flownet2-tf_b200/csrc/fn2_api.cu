@@ -213,4 +213,16 @@ int fn2_downsample_forward(const float* in, float* out, int N, int iH, int iW, i
   return downsample_forward(in, out, N, iH, iW, C, oH, oW, static_cast<cudaStream_t>(stream));
 }
 
+int fn2_downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
+                                 int iW, int C, void* stream) {
+  if (N < 1 || iH < 1 || iW < 1 || C < 1 || num_scales < 1) return FN2_E_BAD_SHAPE;
+  if (!in || !outs || !out_hw || !aligned16(in)) return FN2_E_BAD_POINTER;
+  for (int s = 0; s < num_scales; ++s) {
+    if (out_hw[2 * s] < 1 || out_hw[2 * s + 1] < 1) return FN2_E_BAD_SHAPE;
+    if (out_hw[2 * s] < 2 || out_hw[2 * s + 1] < 2) return FN2_E_DOWNSAMPLE_SIZE;
+    if (!outs[s] || !aligned16(outs[s])) return FN2_E_BAD_POINTER;
+  }
+  return downsample_multi_forward(in, outs, out_hw, num_scales, N, iH, iW, C, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

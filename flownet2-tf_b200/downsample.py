@@ -42,3 +42,32 @@ def downsample(tensor, size):
     if isinstance(tensor, torch.Tensor) and tensor.requires_grad:
         return _Downsample.apply(tensor, int(size[0]), int(size[1]))
     return _forward(tensor, size)
+
+
+def downsample_multi(tensor, sizes):
+    """[downsample(tensor, size) for size in sizes] in one pass over ``tensor``.
+
+    The reference's losses downsample the same ground-truth flow to five sizes with five op calls
+    (``flownet_c.py:135-160``); each output here equals the single-size op's.  No gradient, as for ``downsample``.
+    """
+    import ctypes
+    _lib.require_cuda_f32(tensor, "input")
+    if isinstance(tensor, torch.Tensor) and tensor.requires_grad:
+        raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
+    sizes = [list(s) for s in sizes]
+    if not sizes:
+        return []
+    for s in sizes:
+        if len(s) != 2:  # downsample_kernel.cc:19
+            raise ValueError("size must be 2 dimensions")
+        if int(s[0]) < 1 or int(s[1]) < 1:
+            raise ValueError("Downsample: output dimensions must be positive")
+    N, H, W, C = tensor.shape
+    outs = [torch.empty((N, int(s[0]), int(s[1]), C), dtype=torch.float32, device=tensor.device) for s in sizes]
+    ptrs = (ctypes.c_void_p * len(outs))(*[o.data_ptr() for o in outs])
+    hw = (ctypes.c_int * (2 * len(outs)))(*[int(v) for s in sizes for v in s])
+    with torch.cuda.device(tensor.device):
+        st = _lib.lib().fn2_downsample_multi_forward(tensor.data_ptr(), ptrs, hw, len(outs), N, H, W, C,
+                                                     _lib.current_stream_ptr(tensor.device))
+    _lib.check(st, "Downsample")
+    return outs

@@ -142,6 +142,15 @@ FN2_API int fn2_flow_warp_backward(const float* image, const float* flow, const 
 FN2_API int fn2_downsample_forward(const float* input, float* output, int N, int in_h, int in_w, int C, int out_h,
                            int out_w, void* stream);
 
+/* Multi-scale downsample.  Replaces the five consecutive downsample() calls that every loss of
+ * the reference makes on the same ground-truth flow (flownet_c.py:135-160, flownet_s.py:128-153, flownet_sd.py:129-154;
+ * edge maps likewise in the HFEM losses, utils.py:227-339): outputs[s] = downsample(input, [out_hw[2s], out_hw[2s+1]])
+ * for s < num_scales, every scale computed directly from `input` with the arithmetic of fn2_downsample_forward, the
+ * input read from HBM once.  `outputs` (num_scales device pointers) and `out_hw` (2*num_scales ints) are HOST arrays,
+ * consumed before the call returns. */
+FN2_API int fn2_downsample_multi_forward(const float* input, float* const* outputs, const int* out_hw, int num_scales,
+                                 int N, int in_h, int in_w, int C, void* stream);
+
 /* Number of kernel launches (library kernels, not memsets) enqueued by this process so far; bench.py reports the
  * difference over its timed region as `gpu_launches`. */
 FN2_API unsigned long long fn2_launch_count(void);

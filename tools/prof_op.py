@@ -28,6 +28,8 @@ else:
         fn = lambda: fn2.flow_warp(img, flo)
     elif op == "warp_bwd":
         fn = lambda: fn2.flow_warp_grad(img, flo, gi)
+    elif op == "ds_multi":
+        fn = lambda: fn2.downsample_multi(flo, [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)])
     else:
         oh, ow = [int(v) for v in op[2:].split("x")]
         fn = lambda: fn2.downsample(flo, [oh, ow])

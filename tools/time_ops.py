@@ -83,7 +83,6 @@ if want("warp") or want("down"):
     if want("down"):
         for s in [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]:
             timed("downsample_%dx%d" % s, lambda i, s=s: fn2.downsample(FLO[i], list(s)), flo + N * s[0] * s[1] * 2 * f)
-        if hasattr(fn2, "downsample_pyramid"):
-            sizes = [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]
-            timed("downsample_pyramid", lambda i: fn2.downsample_pyramid(FLO[i], sizes),
-                  flo + sum(N * h * w * 2 * f for h, w in sizes))
+        sizes = [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]
+        timed("downsample_multi", lambda i: fn2.downsample_multi(FLO[i], sizes),
+              flo + sum(N * h * w * 2 * f for h, w in sizes))
