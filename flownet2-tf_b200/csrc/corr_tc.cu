@@ -21,6 +21,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = epilogue
 // (two warps per TMEM lane quadrant, taking alternate b-rows).
+#include <cstdlib>
 #include "fn2_tc.cuh"
 
 namespace fn2 {
@@ -42,12 +43,14 @@ constexpr int STG_FLOATS = 32 * 33;  // per-warp transposed staging tile [b colu
 struct TcParams {
   CUtensorMap a[4];
   CUtensorMap b[4];
+  CUtensorMap b2[4];  // the same tensor with boxes of 2 rows (CTA-pair kernel: half a block per CTA)
   float* out;
   int N, H, W, C, D, s2, ncls;
   int Hc[2], Wc[2];   // class-space extent per parity
   int Hcb[2];         // class-space rows of b (>= Hc + boff when b carries row halos)
   int boff;           // class-space row of b that a-row 0 meets at displacement 0 (halo_top / s2)
   int TY, TX;         // tiles per class (upper bound over classes)
+  int TYP;            // pairs of row tiles per class (CTA-pair kernel)
   int nkc;            // C / 32
   float sumelems;
 };
@@ -263,6 +266,234 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
   }
 }
 
+// ---- CTA-pair forward (cta_group::2), narrow images (one column tile per class) ---------------------------------
+// Two CTAs of a cluster own 8 consecutive class-rows of a (4 each, resident as before) and share every streamed b
+// block: each CTA loads only HALF of a block (2 b-rows x 32 columns x 32 channels = 8 KB per chunk) and one
+// tcgen05.mma.cta_group::2 (M 256, N 128, K 8) multiplies both a tiles by the whole block, reading the two halves from
+// the two CTAs' shared memory.  Per a tile the L2 -> shared-memory fill drops from <= 896 KB to <= 576 KB (the pair
+// needs b-rows y0-10 .. y0+17: 7 blocks of 64 KB per CTA instead of 6 of 128 KB), which is what bounds this kernel.
+// Barrier protocol: the leader (rank 0) owns full[] (both CTAs' TMA bytes land on it) and tmem_empty[] (both CTAs'
+// epilogue warps arrive on it); empty[] and tmem_full[] live in each CTA and are signalled by multicast commits.
+#ifdef FN2_TIMELINE
+__device__ long long g_tl[1024 * 64];
+#define TL(slot) do { if (blockIdx.x < 1024) g_tl[blockIdx.x * 64 + (slot)] = clock64(); } while (0)
+#define TLG(slot) do { if (blockIdx.x < 1024) { unsigned long long gt_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_)); g_tl[blockIdx.x * 64 + (slot)] = (long long)gt_; } } while (0)
+#else
+#define TL(slot) do {} while (0)
+#define TLG(slot) do {} while (0)
+#endif
+constexpr int PSTAGE_BYTES = 64 * 128;   // half a block per CTA and chunk
+constexpr int PNSTAGE = 8;
+
+struct __align__(8) PairBarriers {
+  uint64_t a_full;
+  uint64_t full[PNSTAGE];
+  uint64_t empty[PNSTAGE];
+  uint64_t tmem_full[NBUF];
+  uint64_t tmem_empty[NBUF];
+  uint32_t tmem_base;
+};
+
+template <int R>
+__global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __grid_constant__ TcParams P) {
+  constexpr int GW = 2 * R + 1;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)P.nkc * CHUNK_BYTES;
+  float* sStage = reinterpret_cast<float*>(sB + (size_t)PNSTAGE * PSTAGE_BYTES);
+  PairBarriers* bars = reinterpret_cast<PairBarriers*>(sStage + NEPI * STG_FLOATS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+
+  // ---- which pair of tiles ----
+  int t = blockIdx.x >> 1;
+  const int typ = t % P.TYP; t /= P.TYP;
+  const int cls = t % P.ncls;
+  const int n = t / P.ncls;
+  const int cy = cls / P.s2, cx = cls % P.s2;
+  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
+  const int y0p = typ * 2 * TILE_R;
+  if (y0p >= Hc || Wc < 1) return;   // both CTAs of the pair leave together, before any barrier exists
+  const int y0 = y0p + (int)rank * TILE_R, x0 = 0;
+  const int Hcb = P.Hcb[cy];
+  const int ylast = min(y0p + 2 * TILE_R - 1, Hc - 1);
+  const int s_first = max(0, y0p + P.boff - R);
+  const int s_last = min(Hcb - 1, ylast + P.boff + R);
+  const int nblk = max(0, (s_last - s_first + 1 + 3) / 4);   // blocks of 4 b-rows x 32 b-columns, the same in both CTAs
+  const int nkc = P.nkc;
+  if (threadIdx.x == 0) { TL(0); TLG(1); }
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bars->a_full), 1);
+    for (int i = 0; i < PNSTAGE; ++i) { mbar_init(smem_u32(&bars->full[i]), 1); mbar_init(smem_u32(&bars->empty[i]), 1); }
+    for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), 2 * NEPI); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc_pair(smem_u32(&bars->tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // the peer's barriers exist before anything is signalled on them
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+  if (threadIdx.x == 0) TL(2);
+
+  if (warp == 0) {
+    // ================================ TMA producer (both CTAs) ================================
+    if (lane == 0) {
+      const uint32_t a_full0 = mapa_u32(smem_u32(&bars->a_full), 0);
+      if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_full), 2u * (uint32_t)nkc * CHUNK_BYTES);
+      const int ya = y0 < Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
+      for (int kc = 0; kc < nkc; ++kc)
+        tma_load_4d_pair(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls], a_full0, kc * KCH, x0, ya, n);
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int srow = s_first + blk * 4 + 2 * (int)rank;   // this CTA's two b-rows of the block
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % PNSTAGE;
+          mbar_wait(smem_u32(&bars->empty[stage]), ((it / PNSTAGE) & 1) ^ 1);
+          if (rank == 0) mbar_expect_tx(smem_u32(&bars->full[stage]), 2u * PSTAGE_BYTES);
+          tma_load_4d_pair(smem_u32(sB + (size_t)stage * PSTAGE_BYTES), &P.b2[cls],
+                           mapa_u32(smem_u32(&bars->full[stage]), 0), kc * KCH, x0, srow, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (leader only) ================================
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = idesc_tf32(256, BLK_N);
+      mbar_wait(smem_u32(&bars->a_full), 0);
+      tc_fence_after();
+      TL(3);
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int buf = blk % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((blk / NBUF) & 1) ^ 1);
+        tc_fence_after();
+        TL(4 + blk);
+        const uint32_t d_tmem = tmem_base + (uint32_t)buf * BLK_N;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % PNSTAGE;
+          mbar_wait(smem_u32(&bars->full[stage]), (it / PNSTAGE) & 1);
+          tc_fence_after();
+          if (kc == 0) TL(12 + blk);
+          const uint32_t a_addr = smem_u32(sA + (size_t)kc * CHUNK_BYTES);
+          const uint32_t b_addr = smem_u32(sB + (size_t)stage * PSTAGE_BYTES);
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)
+            umma_tf32_pair(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
+                           (uint32_t)((kc | k4) != 0));
+          umma_commit_pair(smem_u32(&bars->empty[stage]), 3);   // frees the stage in both CTAs
+        }
+        umma_commit_pair(smem_u32(&bars->tmem_full[buf]), 3);   // accumulator block complete in both CTAs
+        TL(20 + blk);
+      }
+    }
+  } else {
+    // ================================ epilogue (warps 2..9, both CTAs) ================================
+    const int ew = warp - 2;
+    const int q = warp & 3;              // TMEM lane quadrant this warp may read = a-row of the tile
+    const int half = ew >> 2;            // the two warps of a quadrant take alternate b-rows
+    const int y = y0 + q;
+    float* stg = sStage + ew * STG_FLOATS;
+    const bool row_ok = y < Hc;
+    const int Y = y * P.s2 + cy;
+    const int ncol = min(TILE_C, Wc - x0);
+    const float inv = 1.0f / P.sumelems;
+    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.D;
+    const int pixstride = P.s2 * P.D;
+    const uint32_t tmem_empty0 = mapa_u32(smem_u32(&bars->tmem_empty[0]), 0);
+
+    // per-lane plan for writing one displacement row (32 pixels x GW values) coalesced; see corr_tc_fwd_kernel.
+    // rd = staging word to read (the never-written pad word 32, zeroed below, for displacements that leave the image
+    // sideways), go = byte offset of the output element from the row's first element.
+    int rd[GW];
+    uint32_t go[GW];
+    uint32_t smask = 0;
+#pragma unroll
+    for (int tt = 0; tt < GW; ++tt) {
+      const int e = tt * 32 + lane;
+      const int cc = e / GW, o = e - cc * GW;
+      const int xb = cc + o - R;
+      const bool xok = (xb >= 0) && (xb < 32);
+      rd[tt] = xok ? xb * 33 + cc : 32;
+      go[tt] = (uint32_t)(cc * pixstride + o) * 4u;
+      smask |= ((cc < ncol) ? 1u : 0u) << tt;
+    }
+    if (lane == 0) stg[32] = 0.f;
+    __syncwarp();
+
+    if (row_ok) {   // displacement rows that point outside the image: zeros, never computed
+      const int yb = y + P.boff;
+      const int dlo = min(GW, max(0, R - yb)) * GW;
+      const int dhi = max(0, min(GW, Hcb - yb + R)) * GW;
+      for (int cc = half; cc < ncol; cc += 2) {
+        float* po = orow0 + (size_t)cc * pixstride;
+        for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
+        for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
+      }
+    }
+
+    for (int blk = 0; blk < nblk; ++blk) {
+      const int buf = blk % NBUF;
+      mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
+      tc_fence_after();
+      if (ew == 0 && lane == 0) TL(28 + blk);
+#pragma unroll
+      for (int h2 = 0; h2 < 2; ++h2) {
+        const int br = half + 2 * h2;
+        const int s = s_first + blk * 4 + br;
+        const int p = s - (y + P.boff);
+        if (row_ok && p >= -R && p <= R && s < Hcb) {   // warp-uniform
+          float v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];
+          __syncwarp();
+          char* orow = reinterpret_cast<char*>(orow0 + (p + R) * GW);
+          if (ncol == TILE_C) {   // full tile (warp-uniform): straight-line load, scale, store
+#pragma unroll
+            for (int tt = 0; tt < GW; ++tt)
+              *reinterpret_cast<float*>(orow + go[tt]) = stg[rd[tt]] * inv;
+          } else {
+#pragma unroll
+            for (int tt = 0; tt < GW; ++tt)
+              if ((smask >> tt) & 1u) *reinterpret_cast<float*>(orow + go[tt]) = stg[rd[tt]] * inv;
+          }
+          __syncwarp();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(tmem_empty0 + (uint32_t)buf * 8u);
+      if (ew == 0 && lane == 0) TL(36 + blk);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x == 0) TL(44);
+  cluster_sync_all();          // neither CTA may go while the other can still touch its shared memory / barriers
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+  if (threadIdx.x == 32) {
+    TL(45); TLG(46);
+#ifdef FN2_TIMELINE
+    unsigned sm_; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));
+    if (blockIdx.x < 1024) { g_tl[blockIdx.x * 64 + 47] = sm_; g_tl[blockIdx.x * 64 + 48] = nblk; }
+#endif
+  }
+}
+
+size_t fwd_pair_smem_bytes(int nkc) {
+  return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)PNSTAGE * PSTAGE_BYTES + (size_t)NEPI * STG_FLOATS * sizeof(float) +
+         sizeof(PairBarriers);
+}
+
 size_t fwd_smem_bytes(int nkc) {
   return 1024 + (size_t)nkc * CHUNK_BYTES + (size_t)NSTAGE * CHUNK_BYTES + (size_t)NEPI * STG_FLOATS * sizeof(float) +
          sizeof(Barriers);
@@ -296,19 +527,21 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   }
   P.TY = (P.Hc[0] + TILE_R - 1) / TILE_R;
   P.TX = (P.Wc[0] + TILE_C - 1) / TILE_C;
+  P.TYP = (P.TY + 1) / 2;
   P.nkc = g.C / KCH;
   P.sumelems = (float)g.C;
   for (int cls = 0; cls < P.ncls; ++cls) {
     const int cy = cls / g.s2, cx = cls % g.s2;
     if (P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // empty class (H or W == 1 with s2 == 2): map class 0 instead, never used
-      P.a[cls] = P.a[0]; P.b[cls] = P.b[0];
+      P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; P.b2[cls] = P.b2[0];
       continue;
     }
     if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, TILE_R) ||
-        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 4))
+        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 4) ||
+        !make_class_map(&P.b2[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 2))
       return FN2_E_CUDA;
   }
-  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }
+  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; P.b2[cls] = P.b2[0]; }
   const size_t smem = fwd_smem_bytes(P.nkc);
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
@@ -318,16 +551,44 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
     if (attr_err == cudaSuccess)
       attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       (int)fwd_smem_bytes(MAX_KC));
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(corr_tc_fwd_pair_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)fwd_pair_smem_bytes(MAX_KC));
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  if (P.TX == 1 && !getenv("FN2_NO_PAIR")) {   // narrow images: CTA pairs share every b block
+    const long long pgrid = (long long)g.N * P.ncls * P.TYP * 2;
+    if (pgrid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pgrid);
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = fwd_pair_smem_bytes(P.nkc);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, corr_tc_fwd_pair_kernel<10>, P);
+    if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
+    return after_launch();
+  }
   if (P.TX > 1)
     corr_tc_fwd_kernel<10, true><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   else
     corr_tc_fwd_kernel<10, false><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   return after_launch();
 }
+
+#ifdef FN2_TIMELINE
+extern "C" __attribute__((visibility("default"))) int fn2_debug_timeline(long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_tl, sizeof(long long) * 1024 * 64);
+}
+#endif
 
 int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
                      int precision, void*, size_t, cudaStream_t st) {

@@ -57,7 +57,7 @@ def timed(name, fn, nbytes, reps=5):
 
 
 def want(n):
-    return only is None or any(n.startswith(o) for o in only)
+    return only is None or any(n.startswith(o) or o.startswith(n) for o in only)
 
 
 f = 4
