@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t a_full = smem_u32(&bars->a_full);
       mbar_expect_tx(a_full, (uint32_t)nkc * CHUNK_BYTES);
       for (int kc = 0; kc < nkc; ++kc)
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = idesc_tf32(128, BLK_N);
       mbar_wait(smem_u32(&bars->a_full), 0);
       tc_fence_after();
@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
 
   if (warp == 0) {
     // ================================ TMA producer (both CTAs) ================================
-    if (lane == 0) {
+    if (elect_one()) {
       const uint32_t a_full0 = mapa_u32(smem_u32(&bars->a_full), 0);
       if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_full), 2u * (uint32_t)nkc * CHUNK_BYTES);
       const int ya = y0 < Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     }
   } else if (warp == 1) {
     // ================================ MMA issuer (leader only) ================================
-    if (lane == 0 && rank == 0) {
+    if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = idesc_tf32(256, BLK_N);
       mbar_wait(smem_u32(&bars->a_full), 0);
       tc_fence_after();

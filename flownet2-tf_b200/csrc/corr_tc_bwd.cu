@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
 
   if (warp == 0) {
     // ================================ TMA producer: one source row of X per stage ================================
-    if (lane == 0) {
+    if (elect_one()) {
       const CUtensorMap* map = &P.x[mode][cls];
       for (int it = 0; it < nitems; ++it) {
         const int stage = it % NST;
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    if (elect_one()) {
       // A = X^T: MN-major (channels contiguous), M = 128 channels = 4 chunks (LBO = chunk stride), K = 8 pixel rows.
       // B = G  : mode 0 K-major (N = a-pixel rows, K = b-pixel cols); mode 1 MN-major (N = b-pixel cols, LBO = block
       //          stride, K = a-pixel rows).

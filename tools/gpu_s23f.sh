@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_tc.py tests/test_reference_pin.py tests/test_gpu_strips.py -x -q > gpurun_out/s23f_pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/s23f_pytest.log
+tail -15 gpurun_out/s23f_pytest.log
+timeout 300 python tools/time_ops.py 32 tf32 corr 2>&1 | tail -2
+FN2_NO_PAIR=1 timeout 300 python tools/time_ops.py 32 tf32 corr_fwd 2>&1 | tail -1
+timeout 120 python tools/timeline.py 32 > gpurun_out/timeline_pair.txt 2>&1; tail -9 gpurun_out/timeline_pair.txt
