@@ -286,7 +286,7 @@ constexpr int PSTAGE_BYTES = 64 * 128;   // half a block per CTA and chunk
 constexpr int PNSTAGE = 8;
 
 struct __align__(8) PairBarriers {
-  uint64_t a_full;
+  uint64_t a_chunk[MAX_KC];   // leader: 32 channels of BOTH CTAs' a tiles have landed (block 0 starts on chunk 0)
   uint64_t full[PNSTAGE];
   uint64_t empty[PNSTAGE];
   uint64_t tmem_full[NBUF];
@@ -326,7 +326,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
   if (threadIdx.x == 0) { TL(0); TLG(1); }
 
   if (threadIdx.x == 0) {
-    mbar_init(smem_u32(&bars->a_full), 1);
+    for (int i = 0; i < MAX_KC; ++i) mbar_init(smem_u32(&bars->a_chunk[i]), 1);
     for (int i = 0; i < PNSTAGE; ++i) { mbar_init(smem_u32(&bars->full[i]), 1); mbar_init(smem_u32(&bars->empty[i]), 1); }
     for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), 2 * NEPI); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -343,15 +343,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
   if (warp == 0) {
     // ================================ TMA producer (both CTAs) ================================
     if (elect_one()) {
-      const uint32_t a_full0 = mapa_u32(smem_u32(&bars->a_full), 0);
-      if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_full), 2u * (uint32_t)nkc * CHUNK_BYTES);
       const int ya = y0 < Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
-      for (int kc = 0; kc < nkc; ++kc)
-        tma_load_4d_pair(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls], a_full0, kc * KCH, x0, ya, n);
       int it = 0;
       for (int blk = 0; blk < nblk; ++blk) {
         const int srow = s_first + blk * 4 + 2 * (int)rank;   // this CTA's two b-rows of the block
         for (int kc = 0; kc < nkc; ++kc, ++it) {
+          if (blk == 0) {   // the a tile goes out chunk by chunk, interleaved with block 0 which consumes it in this order
+            if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_chunk[kc]), 2u * CHUNK_BYTES);
+            tma_load_4d_pair(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls],
+                             mapa_u32(smem_u32(&bars->a_chunk[kc]), 0), kc * KCH, x0, ya, n);
+          }
           const int stage = it % PNSTAGE;
           mbar_wait(smem_u32(&bars->empty[stage]), ((it / PNSTAGE) & 1) ^ 1);
           if (rank == 0) mbar_expect_tx(smem_u32(&bars->full[stage]), 2u * PSTAGE_BYTES);
@@ -364,9 +365,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     // ================================ MMA issuer (leader only) ================================
     if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = idesc_tf32(256, BLK_N);
-      mbar_wait(smem_u32(&bars->a_full), 0);
-      tc_fence_after();
-      TL(3);
       int it = 0;
       for (int blk = 0; blk < nblk; ++blk) {
         const int buf = blk % NBUF;
@@ -376,6 +374,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
         const uint32_t d_tmem = tmem_base + (uint32_t)buf * BLK_N;
         for (int kc = 0; kc < nkc; ++kc, ++it) {
           const int stage = it % PNSTAGE;
+          if (blk == 0) mbar_wait(smem_u32(&bars->a_chunk[kc]), 0);
           mbar_wait(smem_u32(&bars->full[stage]), (it / PNSTAGE) & 1);
           tc_fence_after();
           if (kc == 0) TL(12 + blk);
