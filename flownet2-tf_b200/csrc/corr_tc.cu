@@ -21,6 +21,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-9 = epilogue
 // (two warps per TMEM lane quadrant, taking alternate b-rows).
+#include <algorithm>
 #include <cstdlib>
 #include "fn2_tc.cuh"
 
@@ -51,6 +52,9 @@ struct TcParams {
   int boff;           // class-space row of b that a-row 0 meets at displacement 0 (halo_top / s2)
   int TY, TX;         // tiles per class (upper bound over classes)
   int TYP;            // pairs of row tiles per class (CTA-pair kernel)
+  // Tail split (CTA-pair kernel): pair tiles >= n_full -- the ones that would run alone in a last, mostly empty wave --
+  // are cut into split_units pieces of split_g b blocks each; every piece loads the a tile again.
+  int n_full, split_units, split_g;
   int nkc;            // C / 32
   float sumelems;
 };
@@ -309,6 +313,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
 
   // ---- which pair of tiles ----
   int t = blockIdx.x >> 1;
+  int part = -1;
+  if (t >= P.n_full) {
+    const int u = t - P.n_full;
+    t = P.n_full + u / P.split_units;
+    part = u % P.split_units;
+  }
   const int typ = t % P.TYP; t /= P.TYP;
   const int cls = t % P.ncls;
   const int n = t / P.ncls;
@@ -319,9 +329,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
   const int y0 = y0p + (int)rank * TILE_R, x0 = 0;
   const int Hcb = P.Hcb[cy];
   const int ylast = min(y0p + 2 * TILE_R - 1, Hc - 1);
-  const int s_first = max(0, y0p + P.boff - R);
+  int s_first = max(0, y0p + P.boff - R);
   const int s_last = min(Hcb - 1, ylast + P.boff + R);
-  const int nblk = max(0, (s_last - s_first + 1 + 3) / 4);   // blocks of 4 b-rows x 32 b-columns, the same in both CTAs
+  int nblk = max(0, (s_last - s_first + 1 + 3) / 4);   // blocks of 4 b-rows x 32 b-columns, the same in both CTAs
+  const bool first_part = part <= 0;                   // the piece that also writes the out-of-image zeros
+  if (part >= 0) {
+    const int lo = part * P.split_g;
+    if (lo >= nblk && part > 0) return;                // both CTAs: this tile has fewer blocks than pieces
+    s_first += lo * 4;
+    nblk = max(0, min(P.split_g, nblk - lo));
+  }
   const int nkc = P.nkc;
   if (threadIdx.x == 0) { TL(0); TLG(1); }
 
@@ -424,7 +441,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     if (lane == 0) stg[32] = 0.f;
     __syncwarp();
 
-    if (row_ok) {   // displacement rows that point outside the image: zeros, never computed
+    if (row_ok && first_part) {   // displacement rows that point outside the image: zeros, never computed
       const int yb = y + P.boff;
       const int dlo = min(GW, max(0, R - yb)) * GW;
       const int dhi = max(0, min(GW, Hcb - yb + R)) * GW;
@@ -558,7 +575,29 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   if (P.TX == 1 && !getenv("FN2_NO_PAIR")) {   // narrow images: CTA pairs share every b block
-    const long long pgrid = (long long)g.N * P.ncls * P.TYP * 2;
+    // Tail split: with `slots` CTA pairs resident at a time, the last npairs % slots pair tiles would run alone in
+    // a final wave; cut each into pieces of g blocks (smallest g whose pieces all fit in that wave).
+    static int slots = 0;
+    if (slots == 0) {
+      int dev = 0, sms = 148;
+      if (cudaGetDevice(&dev) == cudaSuccess) (void)cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      slots = sms / 2 > 0 ? sms / 2 : 1;
+    }
+    const long long npairs = (long long)g.N * P.ncls * P.TYP;
+    const int rows_max = std::min(P.Hcb[0], 2 * TILE_R + 2 * 10);
+    const int maxblk = (rows_max + 3) / 4;
+    const int tail_tiles = (int)(npairs % slots);
+    P.n_full = (int)npairs; P.split_units = 1; P.split_g = maxblk;
+    if (npairs > slots && tail_tiles > 0 && !getenv("FN2_NO_SPLIT")) {
+      for (int gsz = 1; gsz < maxblk; ++gsz) {
+        const int units = (maxblk + gsz - 1) / gsz;
+        if ((long long)tail_tiles * units <= slots) {
+          P.n_full = (int)(npairs - tail_tiles); P.split_units = units; P.split_g = gsz;
+          break;
+        }
+      }
+    }
+    const long long pgrid = ((long long)P.n_full + (npairs - P.n_full) * P.split_units) * 2;
     if (pgrid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)pgrid);
