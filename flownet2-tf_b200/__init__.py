@@ -12,7 +12,8 @@ tensor raises.
 from .correlation import correlation, correlation_grad  # noqa: F401
 from .flow_warp import flow_warp, flow_warp_grad  # noqa: F401
 from .downsample import downsample, downsample_multi  # noqa: F401
+from .flo import read_flo, write_flo  # noqa: F401
 from . import _lib  # noqa: F401
 
 __all__ = ["correlation", "correlation_grad", "flow_warp", "flow_warp_grad", "downsample",
-           "downsample_multi"]
+           "downsample_multi", "read_flo", "write_flo"]

@@ -98,3 +98,50 @@ def oracle_halo_backward(g, a, b_ext, k, md, s1, s2, pad, top, bottom, precision
                                   pad, f64=True)
     return (torch.from_numpy(np.ascontiguousarray(ga[:, top:top + H]).astype(np.float32)),
             torch.from_numpy(gb.astype(np.float32)))
+
+
+# ---- the CPU oracle behind the reference's three op signatures, for running the caller graphs without the kernels ---
+def oracle_ops():
+    """correlation / flow_warp / downsample as torch autograd functions over oracle/ (C restatement, float64 inside).
+    Test infrastructure only: lets the graphs of flownet2_tf_b200.graphs run on CPU with the same weights as on the GPU."""
+    import torch
+    from types import SimpleNamespace
+    from oracle import oracle as o
+
+    def t(x):
+        return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+
+    class Corr(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, a, b, args):
+            ctx.save_for_backward(a, b)
+            ctx.args = args
+            return t(o.c_correlation(a.detach().contiguous().numpy(), b.detach().contiguous().numpy(), *args, f64=True))
+
+        @staticmethod
+        def backward(ctx, g):
+            a, b = ctx.saved_tensors
+            ga, gb = o.c_correlation_grad(g.contiguous().numpy(), a.detach().contiguous().numpy(),
+                                          b.detach().contiguous().numpy(), *ctx.args, f64=True)
+            return t(ga), t(gb), None
+
+    class Warp(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, image, flow):
+            ctx.save_for_backward(image, flow)
+            return t(o.c_flow_warp(image.detach().contiguous().numpy(), flow.detach().contiguous().numpy()))
+
+        @staticmethod
+        def backward(ctx, g):
+            image, flow = ctx.saved_tensors
+            gi, gf = o.c_flow_warp_grad(image.detach().contiguous().numpy(), flow.detach().contiguous().numpy(),
+                                        g.contiguous().numpy())
+            return t(gi), t(gf)
+
+    def downsample(x, size):
+        return t(o.c_downsample(x.detach().contiguous().numpy(), tuple(int(v) for v in size)))
+
+    return SimpleNamespace(
+        correlation=lambda a, b, k, md, s1, s2, pad: Corr.apply(a, b, (k, md, s1, s2, pad)),
+        flow_warp=Warp.apply, downsample=downsample,
+        downsample_multi=lambda x, sizes: [downsample(x, s) for s in sizes])
