@@ -16,8 +16,8 @@ convolutions are torch/cuDNN library calls on channels_last tensors, whose memor
 feature map to one of our NHWC ops is a zero-copy view.  The convolutions are not the hot path of this repo (they are
 what TensorFlow's own conv kernels are in the reference); the three custom ops are.
 
-The ops are injected (``ops=``) so that the parity tests can run the same graph, same weights, with the CPU oracle
-standing in for the kernels; the default is this package's CUDA ops, and there is no fallback.
+The ops are injected (``ops=``) so that the parity tests can run the same graph, same weights, with a CPU
+restatement of the ops standing in for the kernels; the default is this package's CUDA ops, and there is no fallback.
 """
 from types import SimpleNamespace
 
