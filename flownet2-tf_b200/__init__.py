@@ -9,11 +9,11 @@ They call hand-written sm_100a kernels in ``libfn2ops.so`` through a C ABI (``in
 There is no CPU fallback: importing works anywhere, but calling an op without the built library or without a CUDA
 tensor raises.
 """
-from .correlation import correlation, correlation_grad  # noqa: F401
+from .correlation import correlation, correlation_grad, correlation_leaky_concat  # noqa: F401
 from .flow_warp import flow_warp, flow_warp_grad  # noqa: F401
 from .downsample import downsample, downsample_multi  # noqa: F401
 from .flo import read_flo, write_flo  # noqa: F401
 from . import _lib  # noqa: F401
 
 __all__ = ["correlation", "correlation_grad", "flow_warp", "flow_warp_grad", "downsample",
-           "downsample_multi", "read_flo", "write_flo"]
+           "downsample_multi", "correlation_leaky_concat", "read_flo", "write_flo"]

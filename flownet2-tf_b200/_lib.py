@@ -30,6 +30,8 @@ _SIGNATURES = {
     "fn2_correlation_output_shape": (c_int, [c_int] * 7 + [ctypes.POINTER(c_int)] * 3),
     "fn2_correlation_workspace_bytes": (c_size_t, _CORR_GEOM + [c_int, c_int]),
     "fn2_correlation_forward": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, c_void_p, c_size_t, c_void_p]),
+    "fn2_correlation_forward_fused": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, ctypes.c_float, c_int, c_void_p,
+                                              c_size_t, c_void_p]),
     "fn2_correlation_backward": (c_int, [c_void_p] * 5 + _CORR_GEOM + [c_int, c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_forward_halo": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_backward_halo": (c_int, [c_void_p] * 5 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),

@@ -109,3 +109,57 @@ def correlation(input_a, input_b, kernel_size, max_displacement, stride_1, strid
     """
     args = [int(v) for v in (kernel_size, max_displacement, stride_1, stride_2, padding)]
     return _Correlation.apply(input_a, input_b, *args, _prec(precision))
+
+
+# ---- fused forward epilogue ----------------------------------------------------------
+class _CorrelationLeakyConcat(torch.autograd.Function):
+    """cc_relu = LeakyReLU(correlation(a, b, ...)) written straight into channels [offset, offset + D) of ``buf``.
+
+    Backward: d cc = d buf[..., offset:offset+D] * (cc_relu > 0 ? 1 : slope) (torch elementwise), then the
+    CorrelationGrad kernel; the other channels of d buf pass through to ``buf``'s producer."""
+
+    @staticmethod
+    def forward(ctx, a, b, buf, offset, slope, k, md, s1, s2, pad, prec):
+        _check_pair(a, b)
+        _lib.require_cuda_f32(buf, "concat buffer")
+        N, H, W, C = a.shape
+        oh, ow, oc = output_shape(H, W, k, md, s1, s2, pad)
+        if tuple(buf.shape[:3]) != (N, oh, ow) or offset < 0 or offset + oc > buf.shape[3]:
+            raise ValueError("concat buffer %s cannot hold [%d,%d,%d,%d] at channel %d"
+                             % (tuple(buf.shape), N, oh, ow, oc, offset))
+        if offset % 4 != 0:
+            raise ValueError("channel offset must be a multiple of 4 (16-byte alignment of the first element)")
+        geom = (N, H, W, C, k, md, s1, s2, pad)
+        with torch.cuda.device(a.device):
+            ws, nbytes, wsp = _workspace(a, geom, prec, 0)
+            st = _lib.lib().fn2_correlation_forward_fused(
+                a.data_ptr(), b.data_ptr(), buf.data_ptr() + 4 * offset, *geom, int(buf.shape[3]), float(slope), prec,
+                wsp, nbytes, _lib.current_stream_ptr(a.device))
+        _lib.check(st, "Correlation")
+        ctx.mark_dirty(buf)
+        ctx.save_for_backward(a, b, buf)
+        ctx.attrs = (offset, oc, slope, k, md, s1, s2, pad, prec)
+        return buf
+
+    @staticmethod
+    def backward(ctx, gbuf):
+        a, b, buf = ctx.saved_tensors
+        offset, oc, slope, k, md, s1, s2, pad, prec = ctx.attrs
+        cc = buf[..., offset:offset + oc]
+        g = (gbuf[..., offset:offset + oc] * torch.where(cc > 0, 1.0, float(slope))).contiguous()
+        names = {v: n for n, v in _lib.PRECISIONS.items()}
+        ga, gb = correlation_grad(g, a, b, k, md, s1, s2, pad, precision=names[prec])
+        gbuf = gbuf.clone()
+        gbuf[..., offset:offset + oc] = 0
+        return ga, gb, gbuf, None, None, None, None, None, None, None, None
+
+
+def correlation_leaky_concat(input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, padding, buf,
+                             channel_offset, leaky_slope=0.1, *, precision=None):
+    """LeakyReLU(correlation(...)) stored into ``buf[..., channel_offset : channel_offset + D]`` by the kernel's own
+    epilogue; returns ``buf``.  Replaces the three graph nodes of ``flownet_c.py:40-46`` (correlation, LeakyReLU,
+    tf.concat) -- the [N,h,w,441] volume makes no round trip through HBM.  ``buf`` is a contiguous NHWC float32
+    tensor whose other channels (conv_redir's 32) the caller fills, before or after."""
+    args = [int(v) for v in (kernel_size, max_displacement, stride_1, stride_2, padding)]
+    return _CorrelationLeakyConcat.apply(input_a, input_b, buf, int(channel_offset), float(leaky_slope), *args,
+                                         _prec(precision))

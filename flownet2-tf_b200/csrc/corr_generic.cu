@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(256) corr_generic_fwd_kernel(CorrGeom g, const
   const float* an = a + (size_t)n * g.H * g.W * g.C;
   const float* bn = b + (size_t)n * g.bH * g.W * g.C;   // b may carry row halos: its row = a-row + bTop
   const float sumelems = (float)(g.k * g.k * g.C);
-  float* po = out + (size_t)pix * g.D;
+  float* po = out + (size_t)pix * g.oPitch;
 
   for (int d0 = 0; d0 < g.D; d0 += 32) {
     float part[32];
@@ -79,7 +79,10 @@ __global__ void __launch_bounds__(256) corr_generic_fwd_kernel(CorrGeom g, const
       }
     }
     const float tot = transpose_reduce32(part, lane);
-    if (d0 + lane < g.D) po[d0 + lane] = tot / sumelems;
+    if (d0 + lane < g.D) {
+      const float v = tot / sumelems;
+      po[d0 + lane] = v > 0.f ? v : v * g.slope;
+    }
   }
 }
 

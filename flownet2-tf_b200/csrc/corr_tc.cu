@@ -57,7 +57,11 @@ struct TcParams {
   int n_full, split_units, split_g;
   int nkc;            // C / 32
   float sumelems;
+  int opitch;         // floats between consecutive pixels of the output (D, or the width of a concat buffer)
+  float slope;        // fused LeakyReLU: values <= 0 are multiplied by this (1 = plain correlation)
 };
+
+__device__ __forceinline__ float leaky(float x, float slope) { return x > 0.f ? x : x * slope; }
 
 struct __align__(8) Barriers {
   uint64_t a_full;
@@ -174,8 +178,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
     const int ncol = min(TILE_C, Wc - x0);
     const float inv = 1.0f / P.sumelems;
     // first output element of this warp's pixel row (pixel column x0 of the class)
-    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.D;
-    const int pixstride = P.s2 * P.D;    // floats between neighbouring pixels of the class
+    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.opitch;
+    const int pixstride = P.s2 * P.opitch;    // floats between neighbouring pixels of the class
 
     // Per-lane plan for writing one displacement row (32 pixels x GW values, 84-byte runs) coalesced.
     // Block hx covers b-columns [XO, XO + 32) relative to the tile (XO = XO0 + 32 * hx); pixel cc keeps from it the
@@ -250,6 +254,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_kernel(const __grid_c
             for (int tt = 0; tt < NTT; ++tt) {
               float x = stg[rd[hx][tt]];
               x = (WIDE || ((xmask >> tt) & 1u)) ? x * inv : 0.f;
+              x = x > 0.f ? x : x * P.slope;
               if ((smask[hx] >> tt) & 1u) orow[gl[hx][tt]] = x;
             }
             __syncwarp();
@@ -418,8 +423,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     const int Y = y * P.s2 + cy;
     const int ncol = min(TILE_C, Wc - x0);
     const float inv = 1.0f / P.sumelems;
-    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.D;
-    const int pixstride = P.s2 * P.D;
+    const float slope = P.slope;
+    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.opitch;
+    const int pixstride = P.s2 * P.opitch;
     const uint32_t tmem_empty0 = mapa_u32(smem_u32(&bars->tmem_empty[0]), 0);
 
     // per-lane plan for writing one displacement row (32 pixels x GW values) coalesced; see corr_tc_fwd_kernel.
@@ -472,11 +478,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
           if (ncol == TILE_C) {   // full tile (warp-uniform): straight-line load, scale, store
 #pragma unroll
             for (int tt = 0; tt < GW; ++tt)
-              *reinterpret_cast<float*>(orow + go[tt]) = stg[rd[tt]] * inv;
+              *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
           } else {
 #pragma unroll
             for (int tt = 0; tt < GW; ++tt)
-              if ((smask >> tt) & 1u) *reinterpret_cast<float*>(orow + go[tt]) = stg[rd[tt]] * inv;
+              if ((smask >> tt) & 1u) *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
           }
           __syncwarp();
         }
@@ -546,6 +552,8 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   P.TYP = (P.TY + 1) / 2;
   P.nkc = g.C / KCH;
   P.sumelems = (float)g.C;
+  P.opitch = g.oPitch;
+  P.slope = g.slope;
   for (int cls = 0; cls < P.ncls; ++cls) {
     const int cy = cls / g.s2, cx = cls % g.s2;
     if (P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // empty class (H or W == 1 with s2 == 2): map class 0 instead, never used

@@ -43,6 +43,8 @@ static int make_geom(int N, int H, int W, int C, int k, int md, int s1, int s2, 
   g->off = md - pad;
   g->bH = H;
   g->bTop = 0;
+  g->oPitch = g->D;
+  g->slope = 1.0f;
   return FN2_OK;
 }
 
@@ -119,6 +121,19 @@ int fn2_correlation_forward(const float* a, const float* b, float* out, int N, i
   CorrGeom g;
   const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
   if (rc != FN2_OK) return rc;
+  return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
+}
+
+int fn2_correlation_forward_fused(const float* a, const float* b, float* out, int N, int H, int W, int C, int k, int md,
+                                  int s1, int s2, int pad, int out_pixel_pitch, float leaky_slope, int precision,
+                                  void* ws, size_t ws_bytes, void* stream) {
+  CorrGeom g;
+  const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (out_pixel_pitch < g.D) return FN2_E_BAD_SHAPE;
+  if (!(leaky_slope == leaky_slope)) return FN2_E_BAD_PARAM;
+  g.oPitch = out_pixel_pitch;
+  g.slope = leaky_slope;
   return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
 }
 

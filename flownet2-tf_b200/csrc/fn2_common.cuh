@@ -20,6 +20,11 @@ struct CorrGeom {
   // Row halos (fn2_correlation_*_halo, strip partitioning): input_b / backprops_b have bH >= H rows and row y of
   // input_a lines up with row y + bTop of input_b.  Plain calls: bH == H, bTop == 0.
   int bH, bTop;
+  // Fused forward epilogue (fn2_correlation_forward_fused): floats between consecutive output pixels (D for a plain
+  // [N,oH,oW,D] tensor, more when the volume is written into a wider concat buffer) and the LeakyReLU slope applied to
+  // non-positive values (1 = none).
+  int oPitch;
+  float slope;
 };
 
 // Records a launch for fn2_launch_count() and returns the status of the launch that was just made.

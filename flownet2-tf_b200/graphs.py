@@ -30,14 +30,17 @@ LOSS_WEIGHTS = (0.32, 0.08, 0.02, 0.01, 0.005)   # predict_flow6 .. predict_flow
 
 def default_ops(precision="tf32"):
     """This package's CUDA ops behind the reference's three signatures (+ the fused multi-scale downsample)."""
-    from .correlation import correlation as _correlation
+    from .correlation import correlation as _correlation, correlation_leaky_concat as _fused
     from .flow_warp import flow_warp as _flow_warp
     from .downsample import downsample as _downsample, downsample_multi as _downsample_multi
 
     def corr(a, b, k, md, s1, s2, pad):
         return _correlation(a, b, k, md, s1, s2, pad, precision=precision)
+
+    def corr_fused(a, b, k, md, s1, s2, pad, buf, offset, slope):
+        return _fused(a, b, k, md, s1, s2, pad, buf, offset, slope, precision=precision)
     return SimpleNamespace(correlation=corr, flow_warp=_flow_warp, downsample=_downsample,
-                           downsample_multi=_downsample_multi)
+                           downsample_multi=_downsample_multi, correlation_leaky_concat=corr_fused)
 
 
 def leaky_relu(x):
@@ -187,9 +190,18 @@ class FlowNetC(nn.Module):
         c2 = self.conv2(c1)
         c3 = self.conv3(c2)
         conv_a_2, conv_a_3, conv_b_3 = c2[:n], c3[:n], c3[n:]
-        cc = self.ops.correlation(nhwc(conv_a_3), nhwc(conv_b_3), 1, 20, 1, 2, 20)   # :40
-        cc_relu = leaky_relu(nchw(cc))                                               # :41
-        net = torch.cat([self.conv_redir(conv_a_3), cc_relu], dim=1)                 # :44-46, 32 + 441 channels
+        redir = self.conv_redir(conv_a_3)                                            # :44
+        if hasattr(self.ops, "correlation_leaky_concat"):
+            # correlation + LeakyReLU + concat (:40-46) in the kernel's epilogue: the 441 channels land directly in
+            # the 473-channel buffer behind conv_redir's 32
+            buf = torch.empty((n, c3.shape[2], c3.shape[3], 32 + 441), dtype=c3.dtype, device=c3.device)
+            buf[..., :32] = redir.permute(0, 2, 3, 1)
+            buf = self.ops.correlation_leaky_concat(nhwc(conv_a_3), nhwc(conv_b_3), 1, 20, 1, 2, 20, buf, 32, 0.1)
+            net = nchw(buf)
+        else:
+            cc = self.ops.correlation(nhwc(conv_a_3), nhwc(conv_b_3), 1, 20, 1, 2, 20)   # :40
+            cc_relu = leaky_relu(nchw(cc))                                               # :41
+            net = torch.cat([redir, cc_relu], dim=1)                                     # :44-46, 32 + 441 channels
         conv3_1 = self.conv3_1(net)
         conv4_1 = self.conv4_1(self.conv4(conv3_1))
         conv5_1 = self.conv5_1(self.conv5(conv4_1))

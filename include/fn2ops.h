@@ -85,6 +85,18 @@ FN2_API int fn2_correlation_forward(const float* input_a, const float* input_b, 
                             int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
                             int precision, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Correlation with the two steps that follow it in FlowNetC fused into the store:
+ *   cc_relu = LeakyReLU(correlation(conv_a_3, conv_b_3, ...))            flownet_c.py:40-41, utils.py:401-405
+ *   net     = tf.concat([netA_conv, cc_relu], axis=3)                    flownet_c.py:44-46
+ * `output` points at the first correlation channel of pixel (0,0,0) INSIDE the wider buffer (e.g. concat + 32 for the
+ * 32 conv_redir channels), `out_pixel_pitch` is that buffer's channel count (473), and values <= 0 are multiplied by
+ * `leaky_slope` (0.1; 1 = no activation).  Only the D correlation channels of every pixel are written.  With
+ * out_pixel_pitch == D and leaky_slope == 1 this is fn2_correlation_forward. */
+FN2_API int fn2_correlation_forward_fused(const float* input_a, const float* input_b, float* output, int N, int H, int W,
+                                  int C, int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
+                                  int out_pixel_pitch, float leaky_slope, int precision, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+
 /* Replaces REGISTER_OP("CorrelationGrad") + CorrelationGradKernel<GPUDevice>::Compute
  * (correlation_op.cc:64-82, correlation_grad_kernel.cc:15-159) and CorrelationGradA/B
  * (correlation_grad_kernel.cu.cc:191-259).  One launch set for the whole batch; no atomics; both gradients

@@ -45,7 +45,7 @@ def test_flownet_c_forward_and_training_step_match_the_oracle_graph(precision):
     assert _epe(out_g["flow"].cpu(), out_c["flow"]) <= 1e-3                     # north_star: 1e-3 EPE
     loss_c, _ = G.multiscale_loss(gt, out_c, cpu.ops)
     loss_g, _ = G.multiscale_loss(gt.cuda(), out_g, gpu.ops)
-    assert abs(float(loss_g) - float(loss_c)) <= 1e-3 * max(1.0, abs(float(loss_c)))
+    assert abs(float(loss_g.detach()) - float(loss_c.detach())) <= 1e-3 * max(1.0, abs(float(loss_c.detach())))
     loss_c.backward()
     loss_g.backward()
     # gradients that flow back THROUGH the correlation (conv1..3 of both towers) and around it
