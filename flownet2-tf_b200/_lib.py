@@ -36,6 +36,7 @@ _SIGNATURES = {
     "fn2_correlation_forward_halo": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_backward_halo": (c_int, [c_void_p] * 5 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),
     "fn2_flow_warp_forward": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_void_p]),
+    "fn2_flow_warp_error_forward": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "fn2_flow_warp_backward": (c_int, [c_void_p] * 5 + [c_int] * 4 + [c_void_p]),
     "fn2_downsample_forward": (c_int, [c_void_p] * 2 + [c_int] * 6 + [c_void_p]),
     "fn2_downsample_multi_forward": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)] + [c_int] * 5

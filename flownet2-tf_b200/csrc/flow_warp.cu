@@ -413,6 +413,34 @@ int flow_warp_forward(const float* image, const float* flow, float* out, int N, 
   return after_launch();
 }
 
+namespace {
+// err[pixel] = sqrt(sum_c (reference - warped)^2): the shapes the window kernel does not take
+__global__ void __launch_bounds__(256) channel_diff_norm_kernel(const float* __restrict__ ref,
+                                                                const float* __restrict__ warped,
+                                                                float* __restrict__ err, long long npix, int C) {
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += (long long)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float d = __ldg(ref + p * C + c) - warped[p * C + c];
+      acc += d * d;
+    }
+    err[p] = sqrtf(acc);
+  }
+}
+}  // namespace
+
+int flow_warp_forward_error(const float* image, const float* flow, const float* reference, float* out, float* err, int N,
+                            int H, int W, int C, cudaStream_t st) {
+  if (flow_warp_tile_supported(H, W, C)) return flow_warp_tile_forward_error(image, flow, reference, out, err, N, H, W, C, st);
+  const int rc = flow_warp_forward(image, flow, out, N, H, W, C, st);
+  if (rc != FN2_OK) return rc;
+  const long long npix = (long long)N * H * W;
+  long long blocks = (npix + 255) / 256;
+  if (blocks > 148LL * 16) blocks = 148LL * 16;
+  channel_diff_norm_kernel<<<(unsigned)blocks, 256, 0, st>>>(reference, out, err, npix, C);
+  return after_launch();
+}
+
 int flow_warp_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow, int N,
                        int H, int W, int C, cudaStream_t st) {
   const long long npix = (long long)N * H * W;

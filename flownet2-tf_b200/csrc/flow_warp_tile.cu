@@ -90,12 +90,15 @@ __device__ __forceinline__ Taps make_taps(float fx, float fy, int x, int y, int 
 
 // ------------------------------------------------------------------------------------------------ forward
 // MODE 0: out = warp(image, flow).   MODE 1: flow gradient (needs gout), same gather.
+// MODE 2: MODE 0 plus the brightness error of the stacked nets (flownet_cs.py:24-27, flownet2.py:33-39): gout is
+//         the reference image (input_a) and out2[pixel] = sqrt(sum_c (reference - warped)^2), in the same pass.
 template <int C, int MODE>
 __global__ void __launch_bounds__(NT, 2) warp_tile_gather(const __grid_constant__ CUtensorMap imap,
                                                           const float* __restrict__ image,
                                                           const float* __restrict__ flow,
                                                           const float* __restrict__ gout, float* __restrict__ out,
-                                                          int H, int W, int tilesX, int tilesY) {
+                                                          float* __restrict__ out2, int H, int W, int tilesX,
+                                                          int tilesY) {
   extern __shared__ __align__(128) float win_raw[];
   __shared__ __align__(8) uint64_t bar;
   float* win = align128(win_raw);
@@ -123,7 +126,7 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_gather(const __grid_constant_
     const float4 f23 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2) + 1);
     f[0] = make_float2(f01.x, f01.y); f[1] = make_float2(f01.z, f01.w);
     f[2] = make_float2(f23.x, f23.y); f[3] = make_float2(f23.z, f23.w);
-    if (MODE == 1) {
+    if (MODE >= 1) {
       float gv[PXT * C];
 #pragma unroll
       for (int v = 0; v < C; ++v) {
@@ -169,7 +172,7 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_gather(const __grid_constant_
         }
       }
     }
-    if (MODE == 0) {
+    if (MODE != 1) {
       const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
       const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
 #pragma unroll
@@ -191,10 +194,24 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_gather(const __grid_constant_
       gf[i] = tp.in ? make_float2(bx, by) : make_float2(0.f, 0.f);
     }
   }
-  if (MODE == 0) {
+  if (MODE != 1) {
 #pragma unroll
     for (int v = 0; v < C; ++v)
       reinterpret_cast<float4*>(out + pix * C)[v] = make_float4(res[4 * v], res[4 * v + 1], res[4 * v + 2], res[4 * v + 3]);
+    if (MODE == 2) {
+      float e[PXT];
+#pragma unroll
+      for (int i = 0; i < PXT; ++i) {
+        float acc = 0.f;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float d = g[i][c] - res[i * C + c];
+          acc += d * d;
+        }
+        e[i] = sqrtf(acc);
+      }
+      *reinterpret_cast<float4*>(out2 + pix) = make_float4(e[0], e[1], e[2], e[3]);
+    }
   } else {
     reinterpret_cast<float4*>(out + pix * 2)[0] = make_float4(gf[0].x, gf[0].y, gf[1].x, gf[1].y);
     reinterpret_cast<float4*>(out + pix * 2)[1] = make_float4(gf[2].x, gf[2].y, gf[3].x, gf[3].y);
@@ -291,8 +308,8 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_scatter(const float* __restri
 }
 
 template <int C>
-int launch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, int N, int H, int W,
-                cudaStream_t st) {
+int launch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, float* out2, int N,
+                int H, int W, cudaStream_t st) {
   static std::once_flag once;
   static cudaError_t err = cudaSuccess;
   std::call_once(once, [] {
@@ -300,6 +317,8 @@ int launch_tile(int mode, const float* image, const float* flow, const float* go
     err = cudaFuncSetAttribute(warp_tile_gather<C, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (err == cudaSuccess)
       err = cudaFuncSetAttribute(warp_tile_gather<C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (err == cudaSuccess)
+      err = cudaFuncSetAttribute(warp_tile_gather<C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (err == cudaSuccess)
       err = cudaFuncSetAttribute(warp_tile_scatter<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   });
@@ -311,21 +330,25 @@ int launch_tile(int mode, const float* image, const float* flow, const float* go
   CUtensorMap map;   // over `image`, for the gathers
   if (mode != 2 && !make_row_map(&map, image, N, H, W, C, Win<C>::BW, Win<C>::ROWS)) return FN2_E_CUDA;
   if (mode == 0)
-    warp_tile_gather<C, 0><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, nullptr, out, H, W, tilesX, tilesY);
+    warp_tile_gather<C, 0><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, nullptr, out, nullptr, H, W, tilesX,
+                                                               tilesY);
   else if (mode == 1)
-    warp_tile_gather<C, 1><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, H, W, tilesX, tilesY);
+    warp_tile_gather<C, 1><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, nullptr, H, W, tilesX,
+                                                               tilesY);
+  else if (mode == 3)
+    warp_tile_gather<C, 2><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, out2, H, W, tilesX, tilesY);
   else
     warp_tile_scatter<C><<<(unsigned)blocks, NT, smem, st>>>(flow, gout, out, H, W, tilesX, tilesY);
   return after_launch();
 }
 
 int dispatch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, int N, int H, int W,
-                  int C, cudaStream_t st) {
+                  int C, cudaStream_t st, float* out2 = nullptr) {
   switch (C) {
-    case 1: return launch_tile<1>(mode, image, flow, gout, out, N, H, W, st);
-    case 2: return launch_tile<2>(mode, image, flow, gout, out, N, H, W, st);
-    case 3: return launch_tile<3>(mode, image, flow, gout, out, N, H, W, st);
-    case 4: return launch_tile<4>(mode, image, flow, gout, out, N, H, W, st);
+    case 1: return launch_tile<1>(mode, image, flow, gout, out, out2, N, H, W, st);
+    case 2: return launch_tile<2>(mode, image, flow, gout, out, out2, N, H, W, st);
+    case 3: return launch_tile<3>(mode, image, flow, gout, out, out2, N, H, W, st);
+    case 4: return launch_tile<4>(mode, image, flow, gout, out, out2, N, H, W, st);
     default: return FN2_E_BAD_SHAPE;
   }
 }
@@ -337,6 +360,12 @@ bool flow_warp_tile_supported(int H, int W, int C) { return C >= 1 && C <= 4 && 
 int flow_warp_tile_forward(const float* image, const float* flow, float* out, int N, int H, int W, int C,
                            cudaStream_t st) {
   return dispatch_tile(0, image, flow, nullptr, out, N, H, W, C, st);
+}
+
+// warp + brightness error in one pass (mode 3 of launch_tile = MODE 2 of the gather)
+int flow_warp_tile_forward_error(const float* image, const float* flow, const float* reference, float* out, float* err,
+                                 int N, int H, int W, int C, cudaStream_t st) {
+  return dispatch_tile(3, image, flow, reference, out, N, H, W, C, st, err);
 }
 
 // gimage must already be zero (flow_warp_backward memsets it on the same stream)

@@ -212,6 +212,15 @@ int fn2_flow_warp_forward(const float* image, const float* flow, float* out, int
   return flow_warp_forward(image, flow, out, N, H, W, C, static_cast<cudaStream_t>(stream));
 }
 
+int fn2_flow_warp_error_forward(const float* image, const float* flow, const float* reference, float* out, float* err,
+                                int N, int H, int W, int C, void* stream) {
+  if (N < 1 || H < 1 || W < 1 || C < 1) return FN2_E_BAD_SHAPE;
+  if (!image || !flow || !reference || !out || !err) return FN2_E_BAD_POINTER;
+  if (!aligned16(image) || !aligned16(flow) || !aligned16(reference) || !aligned16(out) || !aligned16(err))
+    return FN2_E_BAD_POINTER;
+  return flow_warp_forward_error(image, flow, reference, out, err, N, H, W, C, static_cast<cudaStream_t>(stream));
+}
+
 int fn2_flow_warp_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
                            int N, int H, int W, int C, void* stream) {
   if (N < 1 || H < 1 || W < 1 || C < 1) return FN2_E_BAD_SHAPE;

@@ -64,6 +64,11 @@ int flow_warp_tile_forward(const float* image, const float* flow, float* out, in
                            cudaStream_t st);
 int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
                             int N, int H, int W, int C, cudaStream_t st);
+int flow_warp_tile_forward_error(const float* image, const float* flow, const float* reference, float* out, float* err,
+                                 int N, int H, int W, int C, cudaStream_t st);
+// flow_warp.cu: warp + per-pixel L2 norm over channels of (reference - warped); any shape
+int flow_warp_forward_error(const float* image, const float* flow, const float* reference, float* out, float* err, int N,
+                            int H, int W, int C, cudaStream_t st);
 int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C, int oH, int oW, cudaStream_t st);
 // downsample_multi.cu: several output sizes of one input in a single pass (host arrays of pointers / sizes)
 int downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,

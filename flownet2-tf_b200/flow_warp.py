@@ -60,3 +60,25 @@ class _FlowWarp(torch.autograd.Function):
 
 def flow_warp(image, flow):
     return _FlowWarp.apply(image, flow)
+
+
+def flow_warp_error(image, flow, reference):
+    """(warped, brightness_error) = (flow_warp(image, flow), sqrt(sum_c (reference - warped)^2, keepdims)) in one pass
+    over the data.  These are the nodes every stacked net runs between two sub-nets
+    (``flownet_cs.py:21-27``, ``flownet_css.py:21-27``, ``flownet2.py:33-39``); there they follow frozen nets and data
+    inputs, so no gradient exists -- tensors that require grad are refused (use ``flow_warp`` + torch ops instead)."""
+    _check(image, flow)
+    _lib.require_cuda_f32(reference, "reference")
+    if reference.shape != image.shape:
+        raise ValueError("reference must have the shape of image")
+    if image.requires_grad or flow.requires_grad or reference.requires_grad:
+        raise LookupError("flow_warp_error is forward-only (the reference never differentiates these nodes)")
+    N, H, W, C = image.shape
+    out = torch.empty_like(image)
+    err = torch.empty((N, H, W, 1), dtype=torch.float32, device=image.device)
+    with torch.cuda.device(image.device):
+        st = _lib.lib().fn2_flow_warp_error_forward(image.data_ptr(), flow.data_ptr(), reference.data_ptr(),
+                                                    out.data_ptr(), err.data_ptr(), N, H, W, C,
+                                                    _lib.current_stream_ptr(image.device))
+    _lib.check(st, "FlowWarp")
+    return out, err

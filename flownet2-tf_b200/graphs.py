@@ -31,7 +31,7 @@ LOSS_WEIGHTS = (0.32, 0.08, 0.02, 0.01, 0.005)   # predict_flow6 .. predict_flow
 def default_ops(precision="tf32"):
     """This package's CUDA ops behind the reference's three signatures (+ the fused multi-scale downsample)."""
     from .correlation import correlation as _correlation, correlation_leaky_concat as _fused
-    from .flow_warp import flow_warp as _flow_warp
+    from .flow_warp import flow_warp as _flow_warp, flow_warp_error as _flow_warp_error
     from .downsample import downsample as _downsample, downsample_multi as _downsample_multi
 
     def corr(a, b, k, md, s1, s2, pad):
@@ -40,7 +40,8 @@ def default_ops(precision="tf32"):
     def corr_fused(a, b, k, md, s1, s2, pad, buf, offset, slope):
         return _fused(a, b, k, md, s1, s2, pad, buf, offset, slope, precision=precision)
     return SimpleNamespace(correlation=corr, flow_warp=_flow_warp, downsample=_downsample,
-                           downsample_multi=_downsample_multi, correlation_leaky_concat=corr_fused)
+                           downsample_multi=_downsample_multi, correlation_leaky_concat=corr_fused,
+                           flow_warp_error=_flow_warp_error)
 
 
 def leaky_relu(x):
@@ -283,6 +284,9 @@ class FlowNetSD(nn.Module):
 def _warp_and_error(ops, inputs, flow_nhwc):
     """flow_warp(input_b, flow) and the brightness error ||input_a - warped||_2 over channels
     (flownet_cs.py:21-27, flownet_css.py:21-27), both NHWC."""
+    a, b = inputs["input_a"], inputs["input_b"]
+    if hasattr(ops, "flow_warp_error") and not (a.requires_grad or b.requires_grad or flow_nhwc.requires_grad):
+        return ops.flow_warp_error(b.contiguous(), flow_nhwc.contiguous(), a.contiguous())   # one pass over the data
     warped = ops.flow_warp(inputs["input_b"].contiguous(), flow_nhwc.contiguous())
     diff = inputs["input_a"] - warped
     return warped, torch.sqrt(torch.sum(diff * diff, dim=3, keepdim=True))

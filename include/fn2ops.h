@@ -138,6 +138,14 @@ FN2_API int fn2_correlation_backward_halo(const float* gradients, const float* i
 FN2_API int fn2_flow_warp_forward(const float* image, const float* flow, float* output, int N, int H, int W, int C,
                           void* stream);
 
+/* FlowWarp with the brightness error that every stacked net computes right after it, in the same pass (SURVEY.md
+ * section 8 f-2):  warped = flow_warp(input_b, flow);  error = sqrt(reduce_sum(square(input_a - warped), axis=3))
+ * (flownet_cs.py:21-27, flownet_css.py:21-27, flownet2.py:33-39).  reference = input_a [N,H,W,C];
+ * output [N,H,W,C] = warped, error [N,H,W,1].  Forward only: in the reference these nodes sit behind frozen nets and
+ * data inputs and are never differentiated. */
+FN2_API int fn2_flow_warp_error_forward(const float* image, const float* flow, const float* reference, float* output,
+                                float* error, int N, int H, int W, int C, void* stream);
+
 /* Replaces REGISTER_OP("FlowWarpGrad") + FlowWarpGradKernel<GPUDevice>::Compute
  * (flow_warp_op.cc:13-22, flow_warp_grad.cc:13-56, launcher flow_warp_grad.cu.cc:90-123) with the two outputs the
  * op declares (the reference allocates both at index 0, flow_warp_grad.cc:36-37, and so cannot run).

@@ -73,3 +73,20 @@ def test_fused_errors():
         fn2.correlation_leaky_concat(a, b, *ARGS, torch.empty(1, 8, 8, 473, device="cuda"), 30)
     with pytest.raises(ValueError):
         fn2.correlation_leaky_concat(a, b, *ARGS, torch.empty(1, 8, 8, 473), 32)
+
+
+@pytest.mark.parametrize("shape", [(2, 384, 512, 3), (1, 37, 52, 3), (1, 20, 30, 3), (1, 16, 24, 8), (2, 33, 64, 1)])
+def test_flow_warp_error_equals_warp_then_norm(shape):
+    from conftest import warp_inputs
+    N, H, W, C = shape
+    image, flow = warp_inputs(N, H, W, C)
+    ref = torch.rand(N, H, W, C, generator=torch.Generator().manual_seed(11))
+    image, flow, ref = image.cuda(), flow.cuda(), ref.cuda()
+    warped, err = fn2.flow_warp_error(image, flow, ref)
+    want_w = fn2.flow_warp(image, flow)
+    assert torch.equal(warped, want_w)
+    want_e = torch.sqrt(((ref - want_w) ** 2).sum(3, keepdim=True))
+    torch.testing.assert_close(err, want_e, rtol=2e-6, atol=1e-7)
+    assert_close(warped.cpu().numpy(), o.c_flow_warp(image.cpu().numpy(), flow.cpu().numpy()), what="warp")
+    with pytest.raises(LookupError):
+        fn2.flow_warp_error(image.clone().requires_grad_(), flow, ref)
