@@ -387,10 +387,16 @@ def main():
                 "correlation_fwd_bwd_hbm_frac": round(
                     (abytes["corr_fwd"] + abytes["corr_bwd"]) / ((per_op_ms["corr_fwd"] + per_op_ms["corr_bwd"]) * 1e-3)
                     / 1e9 / hbm_peak, 4)}
-    prof = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the committed ncu capture
-    if os.path.exists(prof):
+    # DRAM bytes per launch (read + write) from the committed `ncu --set full` captures of these kernels at batch 32
+    # (profiles/traffic.json, written by tools/make_traffic.py); only valid for the batch it was captured at
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof) and B == 32:
         try:
-            roofline["traffic"] = json.load(open(prof)).get(precision, {}).get(dominant)
+            tr = json.load(open(prof)).get(precision, {})
+            roofline["traffic"] = tr.get(dominant)
+            for name in ops:
+                if name in tr:
+                    per_op[name]["dram_mb_ncu"] = round(tr[name] / 1e6, 2)
         except Exception:
             pass
 
