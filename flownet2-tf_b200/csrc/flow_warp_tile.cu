@@ -13,6 +13,7 @@
 // adds; it is then flushed row by row with bulk reduce-adds (cp.reduce.async.bulk .add.f32) instead of 12 scattered
 // atomics per pixel.  Out-of-window taps go to global atomics directly.
 // Backward, flow gradient: a gather like the forward, from the staged image window.
+#include <cstdlib>
 #include <mutex>
 #include "fn2_tc.cuh"
 
@@ -307,6 +308,160 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_scatter(const float* __restri
   }
 }
 
+// ------------------------------------------------------------------------------------- backward: both gradients
+// One kernel for the whole FlowWarpGrad op: flow and gradients are read ONCE and kept in registers; the shared-memory
+// window first holds the image neighbourhood (TMA) for the flow-gradient gather, then -- zeroed -- collects the
+// image-gradient scatter and is flushed with bulk reduce-adds.  gimage must already be zero.
+template <int C>
+__global__ void __launch_bounds__(NT, 2) warp_tile_bwd(const __grid_constant__ CUtensorMap imap,
+                                                       const float* __restrict__ image,
+                                                       const float* __restrict__ flow,
+                                                       const float* __restrict__ gout, float* __restrict__ gflow,
+                                                       float* __restrict__ gimage, int H, int W, int tilesX,
+                                                       int tilesY) {
+  extern __shared__ __align__(128) float win_raw[];
+  __shared__ __align__(8) uint64_t bar;
+  float* win = align128(win_raw);
+  const Tile t = make_tile<C>(tilesX, tilesY);
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bar), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    mbar_expect_tx(smem_u32(&bar), Win<C>::TX_BYTES);
+#pragma unroll
+    for (int b = 0; b < Win<C>::NB; ++b)
+      tma_load_3d(smem_u32(win + b * Win<C>::BOX_FLOATS), &imap, smem_u32(&bar), t.wx0 * C + b * Win<C>::BW, t.wy0,
+                  t.n);
+  }
+  __syncthreads();
+  const int y = t.ty0 + threadIdx.x / (TW / PXT);
+  const int x = t.tx0 + (threadIdx.x % (TW / PXT)) * PXT;
+  const bool live = (y < H) && (x < W);
+  const size_t pix = ((size_t)t.n * H + (live ? y : 0)) * W + (live ? x : 0);
+
+  float2 f[PXT];
+  float gv[PXT * C];
+#pragma unroll
+  for (int i = 0; i < PXT; ++i) f[i] = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < PXT * C; ++i) gv[i] = 0.f;
+  if (live) {
+    const float4 f01 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2));
+    const float4 f23 = __ldg(reinterpret_cast<const float4*>(flow + pix * 2) + 1);
+    f[0] = make_float2(f01.x, f01.y); f[1] = make_float2(f01.z, f01.w);
+    f[2] = make_float2(f23.x, f23.y); f[3] = make_float2(f23.z, f23.w);
+#pragma unroll
+    for (int v = 0; v < C; ++v) {
+      const float4 q = __ldg(reinterpret_cast<const float4*>(gout + pix * C) + v);
+      gv[4 * v] = q.x; gv[4 * v + 1] = q.y; gv[4 * v + 2] = q.z; gv[4 * v + 3] = q.w;
+    }
+  }
+  mbar_wait(smem_u32(&bar), 0);
+
+  // ---- phase 1: flow gradient (flow_warp_grad.cu.cc:55-86), taps from the staged image window ----
+  if (live) {
+    const float* img = image + (size_t)t.n * H * W * C;
+    float2 gf[PXT];
+#pragma unroll
+    for (int i = 0; i < PXT; ++i) {
+      const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
+      float bx = 0.f, by = 0.f;
+      if (tp.in) {
+        float iTL[C], iTR[C], iBL[C], iBR[C];
+        const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
+                           (tp.R < t.wx0 + Win<C>::COLS);
+        if (inwin) {
+          const float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
+          const float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
+          const int dB = (tp.B - tp.T) * Win<C>::BW;
+#pragma unroll
+          for (int c = 0; c < C; ++c) { iTL[c] = pL[c]; iTR[c] = pR[c]; iBL[c] = pL[dB + c]; iBR[c] = pR[dB + c]; }
+        } else {
+          const float* pT = img + ((size_t)tp.T * W + tp.L) * C;
+          const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
+#pragma unroll
+          for (int c = 0; c < C; ++c) {
+            iTL[c] = __ldg(pT + c); iTR[c] = __ldg(pT + dR + c);
+            iBL[c] = __ldg(pT + dB + c); iBR[c] = __ldg(pT + dB + dR + c);
+          }
+        }
+        const float gy = float(tp.B) - tp.y2;  // flow_warp_grad.cu.cc:55
+        const float gx = float(tp.R) - tp.x2;  // :72
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          float tx = gy * (iTR[c] - iTL[c]);
+          tx += (1 - gy) * (iBR[c] - iBL[c]);
+          bx += gv[i * C + c] * tx;
+          float ty = gx * (iBL[c] - iTL[c]);
+          ty += (1 - gx) * (iBR[c] - iTR[c]);
+          by += gv[i * C + c] * ty;
+        }
+      }
+      gf[i] = make_float2(bx, by);
+    }
+    reinterpret_cast<float4*>(gflow + pix * 2)[0] = make_float4(gf[0].x, gf[0].y, gf[1].x, gf[1].y);
+    reinterpret_cast<float4*>(gflow + pix * 2)[1] = make_float4(gf[2].x, gf[2].y, gf[3].x, gf[3].y);
+  }
+  __syncthreads();   // everyone has read the image window
+
+  // ---- phase 2: image gradient (flow_warp_grad.cu.cc:43-53): the window, zeroed, collects the scatter ----
+  for (int i = threadIdx.x; i < Win<C>::NB * Win<C>::BOX_FLOATS / 4; i += NT)
+    reinterpret_cast<float4*>(win)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  __syncthreads();
+  if (live) {
+    float* gimg = gimage + (size_t)t.n * H * W * C;
+#pragma unroll
+    for (int i = 0; i < PXT; ++i) {
+      const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
+      if (!tp.in) continue;
+      const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
+      const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
+      const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
+                         (tp.R < t.wx0 + Win<C>::COLS);
+      if (inwin) {
+        float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
+        float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
+        const int dB = (tp.B - tp.T) * Win<C>::BW;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float gc = gv[i * C + c];
+          atomicAdd(pL + c, gc * cTL);
+          atomicAdd(pR + c, gc * cTR);
+          atomicAdd(pL + dB + c, gc * cBL);
+          atomicAdd(pR + dB + c, gc * cBR);
+        }
+      } else {
+        float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;
+        const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          const float gc = gv[i * C + c];
+          atomicAdd(pT + c, gc * cTL);
+          atomicAdd(pT + dR + c, gc * cTR);
+          atomicAdd(pT + dB + c, gc * cBL);
+          atomicAdd(pT + dB + dR + c, gc * cBR);
+        }
+      }
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the async proxy
+  __syncthreads();
+  if (threadIdx.x < Win<C>::NB * Win<C>::ROWS) {
+    const int b = threadIdx.x / Win<C>::ROWS, r = threadIdx.x - b * Win<C>::ROWS;
+    const int yy = t.wy0 + r;
+    const int fc0 = t.wx0 * C + b * Win<C>::BW;
+    const int lo = max(fc0, 0), hi = min(fc0 + Win<C>::BW, W * C);
+    if (yy >= 0 && yy < H && hi > lo) {
+      float* dst = gimage + ((size_t)t.n * H + yy) * W * C + lo;
+      const uint32_t src = smem_u32(win + b * Win<C>::BOX_FLOATS + r * Win<C>::BW + (lo - fc0));
+      asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                   ::"l"(dst), "r"(src), "r"((uint32_t)(hi - lo) * 4u) : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory stays valid until it was read
+  }
+}
+
 template <int C>
 int launch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, float* out2, int N,
                 int H, int W, cudaStream_t st) {
@@ -321,6 +476,8 @@ int launch_tile(int mode, const float* image, const float* flow, const float* go
       err = cudaFuncSetAttribute(warp_tile_gather<C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (err == cudaSuccess)
       err = cudaFuncSetAttribute(warp_tile_scatter<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (err == cudaSuccess)
+      err = cudaFuncSetAttribute(warp_tile_bwd<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   });
   if (err != cudaSuccess) { note_cuda_error(err); return FN2_E_CUDA; }
   const int tilesX = (W + TW - 1) / TW, tilesY = (H + TH - 1) / TH;
@@ -335,6 +492,8 @@ int launch_tile(int mode, const float* image, const float* flow, const float* go
   else if (mode == 1)
     warp_tile_gather<C, 1><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, nullptr, H, W, tilesX,
                                                                tilesY);
+  else if (mode == 4)   // out = gflow, out2 = gimage
+    warp_tile_bwd<C><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, out2, H, W, tilesX, tilesY);
   else if (mode == 3)
     warp_tile_gather<C, 2><<<(unsigned)blocks, NT, smem, st>>>(map, image, flow, gout, out, out2, H, W, tilesX, tilesY);
   else
@@ -371,6 +530,7 @@ int flow_warp_tile_forward_error(const float* image, const float* flow, const fl
 // gimage must already be zero (flow_warp_backward memsets it on the same stream)
 int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
                             int N, int H, int W, int C, cudaStream_t st) {
+  if (!getenv("FN2_WARP_BWD_SPLIT")) return dispatch_tile(4, image, flow, gout, gflow, N, H, W, C, st, gimage);
   const int rc = dispatch_tile(1, image, flow, gout, gflow, N, H, W, C, st);
   if (rc != FN2_OK) return rc;
   return dispatch_tile(2, nullptr, flow, gout, gimage, N, H, W, C, st);
