@@ -55,6 +55,7 @@ struct TcParams {
   // Tail split (CTA-pair kernel): pair tiles >= n_full -- the ones that would run alone in a last, mostly empty wave --
   // are cut into split_units pieces of split_g b blocks each; every piece loads the a tile again.
   int n_full, split_units, split_g;
+  int nwork;          // pair tiles + pieces (CTA-pair kernel: the work list a persistent pair strides over)
   int nkc;            // C / 32
   float sumelems;
   int opitch;         // floats between consecutive pixels of the output (D, or the width of a concat buffer)
@@ -296,6 +297,7 @@ constexpr int PNSTAGE = 8;
 
 struct __align__(8) PairBarriers {
   uint64_t a_chunk[MAX_KC];   // leader: 32 channels of BOTH CTAs' a tiles have landed (block 0 starts on chunk 0)
+  uint64_t a_free[MAX_KC];    // each CTA: the last block of the tile has read chunk kc of the a tile
   uint64_t full[PNSTAGE];
   uint64_t empty[PNSTAGE];
   uint64_t tmem_full[NBUF];
@@ -303,6 +305,49 @@ struct __align__(8) PairBarriers {
   uint32_t tmem_base;
 };
 
+// One unit of work of the pair kernel: a pair tile (8 class-rows of a), or a piece of one (tail split).
+struct PairWork {
+  int n, cls, cy, cx, Hc, Wc, Hcb, y0p, s_first, nblk;
+  bool first_part, valid;
+};
+
+template <int R>
+__device__ __forceinline__ PairWork pair_work(const TcParams& P, int w) {
+  PairWork k;
+  int t = w, part = -1;
+  if (t >= P.n_full) {
+    const int u = t - P.n_full;
+    t = P.n_full + u / P.split_units;
+    part = u % P.split_units;
+  }
+  const int typ = t % P.TYP; t /= P.TYP;
+  k.cls = t % P.ncls;
+  k.n = t / P.ncls;
+  k.cy = k.cls / P.s2; k.cx = k.cls % P.s2;
+  k.Hc = P.Hc[k.cy]; k.Wc = P.Wc[k.cx]; k.Hcb = P.Hcb[k.cy];
+  k.y0p = typ * 2 * TILE_R;
+  k.first_part = part <= 0;                            // the piece that also writes the out-of-image zeros
+  k.nblk = 0; k.s_first = 0;
+  k.valid = !(k.y0p >= k.Hc || k.Wc < 1);
+  if (!k.valid) return k;                              // this class has fewer row tiles: nothing to do
+  const int ylast = min(k.y0p + 2 * TILE_R - 1, k.Hc - 1);
+  k.s_first = max(0, k.y0p + P.boff - R);
+  const int s_last = min(k.Hcb - 1, ylast + P.boff + R);
+  k.nblk = max(0, (s_last - k.s_first + 1 + 3) / 4);   // blocks of 4 b-rows x 32 b-columns, the same in both CTAs
+  if (part >= 0) {
+    const int lo = part * P.split_g;
+    k.s_first += lo * 4;
+    k.nblk = max(0, min(P.split_g, k.nblk - lo));
+    if (k.nblk == 0 && part > 0) k.valid = false;       // this tile has fewer blocks than pieces
+  }
+  return k;
+}
+
+// Persistent: a pair walks the work list w = pair index, + number of pairs, ...  The three roles keep running
+// counters (ring slot, accumulator buffer, tile) so every barrier's phase carries over from tile to tile; the only
+// tile-to-tile hazard is the resident a tile, whose chunk kc may be overwritten once the LAST block's MMAs of that
+// chunk have completed (a_free[kc], committed by the issuer to both CTAs).  The next tile's a chunks and first b
+// blocks therefore load under the current tile's last block and epilogue, and the prologue is paid once per CTA.
 template <int R>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __grid_constant__ TcParams P) {
   constexpr int GW = 2 * R + 1;
@@ -315,40 +360,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
-
-  // ---- which pair of tiles ----
-  int t = blockIdx.x >> 1;
-  int part = -1;
-  if (t >= P.n_full) {
-    const int u = t - P.n_full;
-    t = P.n_full + u / P.split_units;
-    part = u % P.split_units;
-  }
-  const int typ = t % P.TYP; t /= P.TYP;
-  const int cls = t % P.ncls;
-  const int n = t / P.ncls;
-  const int cy = cls / P.s2, cx = cls % P.s2;
-  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
-  const int y0p = typ * 2 * TILE_R;
-  if (y0p >= Hc || Wc < 1) return;   // both CTAs of the pair leave together, before any barrier exists
-  const int y0 = y0p + (int)rank * TILE_R, x0 = 0;
-  const int Hcb = P.Hcb[cy];
-  const int ylast = min(y0p + 2 * TILE_R - 1, Hc - 1);
-  int s_first = max(0, y0p + P.boff - R);
-  const int s_last = min(Hcb - 1, ylast + P.boff + R);
-  int nblk = max(0, (s_last - s_first + 1 + 3) / 4);   // blocks of 4 b-rows x 32 b-columns, the same in both CTAs
-  const bool first_part = part <= 0;                   // the piece that also writes the out-of-image zeros
-  if (part >= 0) {
-    const int lo = part * P.split_g;
-    if (lo >= nblk && part > 0) return;                // both CTAs: this tile has fewer blocks than pieces
-    s_first += lo * 4;
-    nblk = max(0, min(P.split_g, nblk - lo));
-  }
+  const int pair0 = blockIdx.x >> 1, npairs = gridDim.x >> 1;
   const int nkc = P.nkc;
+  constexpr int x0 = 0;
   if (threadIdx.x == 0) { TL(0); TLG(1); }
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < MAX_KC; ++i) mbar_init(smem_u32(&bars->a_chunk[i]), 1);
+    for (int i = 0; i < MAX_KC; ++i) { mbar_init(smem_u32(&bars->a_chunk[i]), 1); mbar_init(smem_u32(&bars->a_free[i]), 1); }
     for (int i = 0; i < PNSTAGE; ++i) { mbar_init(smem_u32(&bars->full[i]), 1); mbar_init(smem_u32(&bars->empty[i]), 1); }
     for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), 2 * NEPI); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -365,51 +383,64 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
   if (warp == 0) {
     // ================================ TMA producer (both CTAs) ================================
     if (elect_one()) {
-      const int ya = y0 < Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
-      int it = 0;
-      for (int blk = 0; blk < nblk; ++blk) {
-        const int srow = s_first + blk * 4 + 2 * (int)rank;   // this CTA's two b-rows of the block
-        for (int kc = 0; kc < nkc; ++kc, ++it) {
-          if (blk == 0) {   // the a tile goes out chunk by chunk, interleaved with block 0 which consumes it in this order
-            if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_chunk[kc]), 2u * CHUNK_BYTES);
-            tma_load_4d_pair(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[cls],
-                             mapa_u32(smem_u32(&bars->a_chunk[kc]), 0), kc * KCH, x0, ya, n);
+      int it = 0, used = 0;
+      for (int w = pair0; w < P.nwork; w += npairs) {
+        const PairWork k = pair_work<R>(P, w);
+        if (k.nblk == 0) continue;
+        const int y0 = k.y0p + (int)rank * TILE_R;
+        const int ya = y0 < k.Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
+        for (int blk = 0; blk < k.nblk; ++blk) {
+          const int srow = k.s_first + blk * 4 + 2 * (int)rank;   // this CTA's two b-rows of the block
+          for (int kc = 0; kc < nkc; ++kc, ++it) {
+            if (blk == 0) {   // the a tile goes out chunk by chunk, interleaved with block 0 which consumes it in this order
+              if (used > 0) mbar_wait(smem_u32(&bars->a_free[kc]), (used - 1) & 1);   // the previous tile is done with it
+              if (rank == 0) mbar_expect_tx(smem_u32(&bars->a_chunk[kc]), 2u * CHUNK_BYTES);
+              tma_load_4d_pair(smem_u32(sA + (size_t)kc * CHUNK_BYTES), &P.a[k.cls],
+                               mapa_u32(smem_u32(&bars->a_chunk[kc]), 0), kc * KCH, x0, ya, k.n);
+            }
+            const int stage = it % PNSTAGE;
+            mbar_wait(smem_u32(&bars->empty[stage]), ((it / PNSTAGE) & 1) ^ 1);
+            if (rank == 0) mbar_expect_tx(smem_u32(&bars->full[stage]), 2u * PSTAGE_BYTES);
+            tma_load_4d_pair(smem_u32(sB + (size_t)stage * PSTAGE_BYTES), &P.b2[k.cls],
+                             mapa_u32(smem_u32(&bars->full[stage]), 0), kc * KCH, x0, srow, k.n);
           }
-          const int stage = it % PNSTAGE;
-          mbar_wait(smem_u32(&bars->empty[stage]), ((it / PNSTAGE) & 1) ^ 1);
-          if (rank == 0) mbar_expect_tx(smem_u32(&bars->full[stage]), 2u * PSTAGE_BYTES);
-          tma_load_4d_pair(smem_u32(sB + (size_t)stage * PSTAGE_BYTES), &P.b2[cls],
-                           mapa_u32(smem_u32(&bars->full[stage]), 0), kc * KCH, x0, srow, n);
         }
+        ++used;
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer (leader only) ================================
     if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = idesc_tf32(256, BLK_N);
-      int it = 0;
-      for (int blk = 0; blk < nblk; ++blk) {
-        const int buf = blk % NBUF;
-        mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((blk / NBUF) & 1) ^ 1);
-        tc_fence_after();
-        TL(4 + blk);
-        const uint32_t d_tmem = tmem_base + (uint32_t)buf * BLK_N;
-        for (int kc = 0; kc < nkc; ++kc, ++it) {
-          const int stage = it % PNSTAGE;
-          if (blk == 0) mbar_wait(smem_u32(&bars->a_chunk[kc]), 0);
-          mbar_wait(smem_u32(&bars->full[stage]), (it / PNSTAGE) & 1);
+      int it = 0, gb = 0, used = 0;
+      for (int w = pair0; w < P.nwork; w += npairs) {
+        const PairWork k = pair_work<R>(P, w);
+        if (k.nblk == 0) continue;
+        for (int blk = 0; blk < k.nblk; ++blk, ++gb) {
+          const int buf = gb % NBUF;
+          mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((gb / NBUF) & 1) ^ 1);
           tc_fence_after();
-          if (kc == 0) TL(12 + blk);
-          const uint32_t a_addr = smem_u32(sA + (size_t)kc * CHUNK_BYTES);
-          const uint32_t b_addr = smem_u32(sB + (size_t)stage * PSTAGE_BYTES);
+          if (used == 0) TL(4 + blk);
+          const uint32_t d_tmem = tmem_base + (uint32_t)buf * BLK_N;
+          for (int kc = 0; kc < nkc; ++kc, ++it) {
+            const int stage = it % PNSTAGE;
+            if (blk == 0) mbar_wait(smem_u32(&bars->a_chunk[kc]), used & 1);
+            mbar_wait(smem_u32(&bars->full[stage]), (it / PNSTAGE) & 1);
+            tc_fence_after();
+            if (kc == 0 && used == 0) TL(12 + blk);
+            const uint32_t a_addr = smem_u32(sA + (size_t)kc * CHUNK_BYTES);
+            const uint32_t b_addr = smem_u32(sB + (size_t)stage * PSTAGE_BYTES);
 #pragma unroll
-          for (int k4 = 0; k4 < 4; ++k4)
-            umma_tf32_pair(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
-                           (uint32_t)((kc | k4) != 0));
-          umma_commit_pair(smem_u32(&bars->empty[stage]), 3);   // frees the stage in both CTAs
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_tf32_pair(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
+                             (uint32_t)((kc | k4) != 0));
+            umma_commit_pair(smem_u32(&bars->empty[stage]), 3);   // frees the stage in both CTAs
+            if (blk == k.nblk - 1) umma_commit_pair(smem_u32(&bars->a_free[kc]), 3);   // a chunk kc may be replaced
+          }
+          umma_commit_pair(smem_u32(&bars->tmem_full[buf]), 3);   // accumulator block complete in both CTAs
+          if (used == 0) TL(20 + blk);
         }
-        umma_commit_pair(smem_u32(&bars->tmem_full[buf]), 3);   // accumulator block complete in both CTAs
-        TL(20 + blk);
+        ++used;
       }
     }
   } else {
@@ -417,23 +448,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     const int ew = warp - 2;
     const int q = warp & 3;              // TMEM lane quadrant this warp may read = a-row of the tile
     const int half = ew >> 2;            // the two warps of a quadrant take alternate b-rows
-    const int y = y0 + q;
     float* stg = sStage + ew * STG_FLOATS;
-    const bool row_ok = y < Hc;
-    const int Y = y * P.s2 + cy;
-    const int ncol = min(TILE_C, Wc - x0);
     const float inv = 1.0f / P.sumelems;
     const float slope = P.slope;
-    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.opitch;
     const int pixstride = P.s2 * P.opitch;
     const uint32_t tmem_empty0 = mapa_u32(smem_u32(&bars->tmem_empty[0]), 0);
 
     // per-lane plan for writing one displacement row (32 pixels x GW values) coalesced; see corr_tc_fwd_kernel.
     // rd = staging word to read (the never-written pad word 32, zeroed below, for displacements that leave the image
-    // sideways), go = byte offset of the output element from the row's first element.
+    // sideways), go = byte offset of the output element from the row's first element, cq = its pixel column.
     int rd[GW];
     uint32_t go[GW];
-    uint32_t smask = 0;
 #pragma unroll
     for (int tt = 0; tt < GW; ++tt) {
       const int e = tt * 32 + lane;
@@ -442,55 +467,70 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
       const bool xok = (xb >= 0) && (xb < 32);
       rd[tt] = xok ? xb * 33 + cc : 32;
       go[tt] = (uint32_t)(cc * pixstride + o) * 4u;
-      smask |= ((cc < ncol) ? 1u : 0u) << tt;
     }
     if (lane == 0) stg[32] = 0.f;
     __syncwarp();
 
-    if (row_ok && first_part) {   // displacement rows that point outside the image: zeros, never computed
-      const int yb = y + P.boff;
-      const int dlo = min(GW, max(0, R - yb)) * GW;
-      const int dhi = max(0, min(GW, Hcb - yb + R)) * GW;
-      for (int cc = half; cc < ncol; cc += 2) {
-        float* po = orow0 + (size_t)cc * pixstride;
-        for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
-        for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
+    int gb = 0;
+    for (int w = pair0; w < P.nwork; w += npairs) {
+      const PairWork k = pair_work<R>(P, w);
+      if (!k.valid) continue;
+      const int y = k.y0p + (int)rank * TILE_R + q;
+      const bool row_ok = y < k.Hc;
+      const int Y = y * P.s2 + k.cy;
+      const int ncol = min(TILE_C, k.Wc - x0);
+      float* orow0 = P.out + (((size_t)k.n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + k.cx)) * P.opitch;
+      uint32_t smask = 0;                // stores of pixel columns that exist (partial tiles only)
+      if (ncol != TILE_C) {
+#pragma unroll
+        for (int tt = 0; tt < GW; ++tt) smask |= (((tt * 32 + lane) / GW < ncol) ? 1u : 0u) << tt;
       }
-    }
 
-    for (int blk = 0; blk < nblk; ++blk) {
-      const int buf = blk % NBUF;
-      mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
-      tc_fence_after();
-      if (ew == 0 && lane == 0) TL(28 + blk);
-#pragma unroll
-      for (int h2 = 0; h2 < 2; ++h2) {
-        const int br = half + 2 * h2;
-        const int s = s_first + blk * 4 + br;
-        const int p = s - (y + P.boff);
-        if (row_ok && p >= -R && p <= R && s < Hcb) {   // warp-uniform
-          float v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];
-          __syncwarp();
-          char* orow = reinterpret_cast<char*>(orow0 + (p + R) * GW);
-          if (ncol == TILE_C) {   // full tile (warp-uniform): straight-line load, scale, store
-#pragma unroll
-            for (int tt = 0; tt < GW; ++tt)
-              *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
-          } else {
-#pragma unroll
-            for (int tt = 0; tt < GW; ++tt)
-              if ((smask >> tt) & 1u) *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
-          }
-          __syncwarp();
+      if (row_ok && k.first_part) {   // displacement rows that point outside the image: zeros, never computed
+        const int yb = y + P.boff;
+        const int dlo = min(GW, max(0, R - yb)) * GW;
+        const int dhi = max(0, min(GW, k.Hcb - yb + R)) * GW;
+        for (int cc = half; cc < ncol; cc += 2) {
+          float* po = orow0 + (size_t)cc * pixstride;
+          for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
+          for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(tmem_empty0 + (uint32_t)buf * 8u);
-      if (ew == 0 && lane == 0) TL(36 + blk);
+
+      for (int blk = 0; blk < k.nblk; ++blk, ++gb) {
+        const int buf = gb % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), (gb / NBUF) & 1);
+        tc_fence_after();
+        if (ew == 0 && lane == 0 && w == pair0) TL(28 + blk);
+#pragma unroll
+        for (int h2 = 0; h2 < 2; ++h2) {
+          const int br = half + 2 * h2;
+          const int s = k.s_first + blk * 4 + br;
+          const int p = s - (y + P.boff);
+          if (row_ok && p >= -R && p <= R && s < k.Hcb) {   // warp-uniform
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BLK_N + br * 32), v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) stg[j * 33 + lane] = v[j];
+            __syncwarp();
+            char* orow = reinterpret_cast<char*>(orow0 + (p + R) * GW);
+            if (ncol == TILE_C) {   // full tile (warp-uniform): straight-line load, scale, store
+#pragma unroll
+              for (int tt = 0; tt < GW; ++tt)
+                *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
+            } else {
+#pragma unroll
+              for (int tt = 0; tt < GW; ++tt)
+                if ((smask >> tt) & 1u) *reinterpret_cast<float*>(orow + go[tt]) = leaky(stg[rd[tt]] * inv, slope);
+            }
+            __syncwarp();
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(tmem_empty0 + (uint32_t)buf * 8u);
+        if (ew == 0 && lane == 0 && w == pair0) TL(36 + blk);
+      }
     }
   }
 
@@ -506,7 +546,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_pair_kernel(const __g
     TL(45); TLG(46);
 #ifdef FN2_TIMELINE
     unsigned sm_; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));
-    if (blockIdx.x < 1024) { g_tl[blockIdx.x * 64 + 47] = sm_; g_tl[blockIdx.x * 64 + 48] = nblk; }
+    if (blockIdx.x < 1024) { g_tl[blockIdx.x * 64 + 47] = sm_; g_tl[blockIdx.x * 64 + 48] = pair_work<R>(P, pair0).nblk; }
 #endif
   }
 }
@@ -605,8 +645,11 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
         }
       }
     }
-    const long long pgrid = ((long long)P.n_full + (npairs - P.n_full) * P.split_units) * 2;
-    if (pgrid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+    const long long nwork = (long long)P.n_full + (npairs - P.n_full) * P.split_units;
+    if (nwork > 0x3fffffffLL) return FN2_E_BAD_SHAPE;
+    P.nwork = (int)nwork;
+    // persistent: one pair per pair of SMs strides over the work list (FN2_NO_PERSIST: one pair per unit of work)
+    const long long pgrid = 2 * (getenv("FN2_NO_PERSIST") ? nwork : std::min<long long>(nwork, slots));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)pgrid);
     cfg.blockDim = dim3(NTHREADS);
