@@ -91,3 +91,22 @@ def test_halo_entry_points_reject_other_geometries():
         strips.correlation_halo_forward(a, torch.zeros(1, 11, 8, 32, device="cuda"), 1, 20, 1, 2, 20, 3, 0, "fp32")
     with pytest.raises(ValueError, match="input_b must have shape"):
         strips.correlation_halo_forward(a, b, 1, 20, 1, 2, 20, 2, 0, "fp32")
+
+
+def test_nccl_strips_on_two_gpus_match_the_whole_op():
+    """BASELINE config 5 with real NCCL send/recv (needs >= 2 visible GPUs; the single-GPU boxes skip it): every rank's
+    strip of the forward and of both gradients equals the whole op computed on one GPU (tools/strips_nccl.py)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533",
+                          os.path.join(root, "tools", "strips_nccl.py"), "tf32"],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = json.loads([l for l in res.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["gpus"] == 2 and line["max_rel_err_vs_whole_op"] <= 2e-3
