@@ -96,3 +96,24 @@ def test_unsupported_precision_is_an_error_not_a_fallback():
     a = torch.zeros(1, 8, 8, 4, device="cuda")   # C % 32 != 0: no tensor-core tiling
     with pytest.raises(ValueError, match="precision not supported"):
         fn2.correlation(a, a, 1, 2, 1, 2, 2, precision="tf32")
+
+
+@pytest.mark.parametrize("shape", [
+    (40, 47, 61, 64),    # more pair tiles than resident pairs, classes of different sizes (invalid tiles in the list),
+                         # partial column tiles, a tail that is split
+    (75, 24, 32, 32),    # 300 pair tiles on 74 pairs: 4 rounds + a split tail of 4 tiles
+    (37, 16, 32, 128),   # exactly two rounds, no tail (C a power of two: the 1/C scaling stays exact)
+    (3, 48, 64, 256),    # fewer pair tiles than resident pairs (one tile each)
+])
+def test_persistent_pair_forward_is_exact_on_integer_inputs(shape):
+    """The persistent CTA-pair forward walks a work list with running barrier phases; integer inputs make every sum
+    exact, so any tile taken twice, skipped, or computed against a stale a tile shows as a wrong integer."""
+    N, H, W, C = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    a = torch.randint(-3, 4, shape, generator=g).float()
+    b = torch.randint(-3, 4, shape, generator=g).float()
+    out = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
+    np.testing.assert_array_equal(out.cpu().numpy().astype(np.float64), want)
+    out2 = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    assert torch.equal(out, out2)
