@@ -51,6 +51,7 @@ constexpr int TMEM_COLS = 2 * TILE_N;      // two 128-channel halves of the accu
 
 struct BwdParams {
   CUtensorMap x[2][4];  // [mode][class]: mode 0 (da) streams b, mode 1 (db) streams a
+  CUtensorMap o[2][4];  // [mode][class]: the output tensor (da, db), boxes of 32 channels x 32 class pixels, no swizzle
   const float* grad;
   float* out[2];        // da, db
   int N, H, W, C, s2, ncls;
@@ -273,21 +274,40 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     const int qd = warp & 3;        // TMEM lane quadrant this warp may read
     const int e = bw >> 2;          // the NBUILD/4 warps of a quadrant take alternate output rows
     const float inv = P.inv;
+    // One TMEM load is [32 channels (lanes)] x [32 output pixels of one row]: exactly one TMA store box.  The warp
+    // writes it to shared memory as [pixel][channel] (lane = channel: conflict-free 128-byte rows) and one lane hands it
+    // to the TMA unit, which also clips the columns and keeps the LSU out of the store path.  Staging: two 4 KB boxes
+    // per warp in the drained X ring.
+    const uint32_t stg = smem_u32(sX) + (uint32_t)bw * 8192u;
+    const CUtensorMap* omap = &P.o[mode][cls];
+    int nb = 0;
     for (int h = 0; h < P.nhalf; ++h) {
-      const int ch = h * 128 + qd * 32 + lane;
+      const int c0 = h * 128 + qd * 32;
+      if (c0 >= P.C) break;         // warp-uniform
       for (int qq = e; qq < TILE_R; qq += NBUILD / 4) {
         const int row = r0 + qq;
         if (row >= Hout) continue;  // warp-uniform
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * TILE_N + qq * 32), v);
-        float* orow = outp + (((size_t)n * Hfull + (size_t)(row * P.s2 + cy)) * P.W + cx + (size_t)x0 * P.s2) * P.C + ch;
-        if (ch < P.C) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (j < ncol) orow[(size_t)j * P.s2 * P.C] = v[j] * inv;
+        const uint32_t buf = stg + (uint32_t)(nb & 1) * 4096u;
+        if (nb >= 2) {
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
         }
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          asm volatile("st.shared.f32 [%0], %1;" ::"r"(buf + (uint32_t)(lane * 4 + j * 128)), "f"(v[j] * inv)
+                       : "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_4d(omap, buf, c0, x0, row, n);
+          tma_store_commit();
+        }
+        ++nb;
       }
     }
+    if (lane == 0) tma_store_wait_read<0>();   // shared memory stays valid until it was read
   }
 
   tc_fence_before();
@@ -338,10 +358,18 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
       const int srcHc = mode ? P.Hc[cy] : P.Hcb[cy];
       if (cls >= P.ncls || srcHc < 1 || P.Wc[cx] < 1) {  // unused / empty class: any valid map, never dereferenced
         P.x[mode][cls] = P.x[mode][0];
+        P.o[mode][cls] = P.o[mode][0];
         continue;
       }
       if (!make_class_map(&P.x[mode][cls], src, g.N, srcH, g.W, g.C, g.s2, cy, cx, srcHc, P.Wc[cx], TILE_C, 1,
                           CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))
+        return FN2_E_CUDA;
+      float* dst = mode ? gb : ga;
+      const int dstH = mode ? g.bH : g.H;
+      const int dstHc = mode ? P.Hcb[cy] : P.Hc[cy];
+      if (dstHc < 1) { P.o[mode][cls] = P.o[mode][0]; continue; }
+      if (!make_class_map(&P.o[mode][cls], dst, g.N, dstH, g.W, g.C, g.s2, cy, cx, dstHc, P.Wc[cx], TILE_C, 1,
+                          CU_TENSOR_MAP_SWIZZLE_NONE))
         return FN2_E_CUDA;
     }
   }

@@ -117,3 +117,26 @@ def test_persistent_pair_forward_is_exact_on_integer_inputs(shape):
     np.testing.assert_array_equal(out.cpu().numpy().astype(np.float64), want)
     out2 = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
     assert torch.equal(out, out2)
+
+
+@pytest.mark.parametrize("shape", [
+    (14, 47, 61, 64),    # 336 tiles on 148 CTAs: every CTA walks over several tiles, ragged classes, partial tiles
+    (37, 16, 32, 128),   # exactly two tiles per CTA, one row tile per class
+    (6, 20, 140, 32),    # wide classes: three column tiles, two 32-pixel items per source row
+    (3, 48, 64, 256),    # fewer tiles than CTAs (one tile each)
+])
+def test_persistent_backward_is_exact_on_integer_inputs(shape):
+    """The persistent backward kernel carries its stage ring, row barriers and accumulator from tile to tile; integer
+    inputs make every sum exact (C is a power of two), so a stale G block, an undrained accumulator row or a tile
+    taken twice shows as a wrong number."""
+    N, H, W, C = shape
+    g = torch.Generator().manual_seed(sum(shape))
+    a = torch.randint(-3, 4, shape, generator=g).float()
+    b = torch.randint(-3, 4, shape, generator=g).float()
+    gr = torch.randint(-3, 4, (N, H, W, 441), generator=g).float()
+    ga, gb = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    wa, wb = o.c_correlation_grad(gr.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
+    np.testing.assert_array_equal(ga.cpu().numpy().astype(np.float64), wa)
+    np.testing.assert_array_equal(gb.cpu().numpy().astype(np.float64), wb)
+    ga2, gb2 = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    assert torch.equal(ga, ga2) and torch.equal(gb, gb2)
