@@ -1,14 +1,14 @@
 """DRAM traffic per launch of every kernel of the hot path, from the `ncu --set full` captures in gpurun_out/
-(tools/gpu_s23k.sh), written to profiles/traffic.json for bench.py's `roofline.traffic`, plus one text summary per
+(tools/gpu_s24z.sh), written to profiles/traffic.json for bench.py's `roofline.traffic`, plus one text summary per
 capture under profiles/.   python tools/make_traffic.py <round tag, e.g. r01_g>"""
 import csv, io, json, os, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
 CAPS = {  # op -> captures (one kernel each) whose launches make up the op
     "corr_fwd": ["corr_fwd"], "corr_bwd": ["corr_bwd"], "warp_fwd": ["warp_fwd"],
-    "warp_bwd": ["warp_bwd_gather", "warp_bwd_scatter"], "downsample": ["ds_multi"]}
+    "warp_bwd": ["warp_bwd"], "downsample": ["ds_multi"]}
 out = {"tf32": {}, "kernels": {}, "how": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full "
-       "--clock-control none, batch 32 (tools/gpu_s23k.sh); per op = sum over the op's kernels (memset of warp_bwd not captured)"}
+       "--clock-control none, batch 32 (tools/gpu_s24z.sh); per op = sum over the op's kernels (memset of warp_bwd not captured; warp_bwd is the fused warp_tile_bwd kernel)"}
 for op, caps in CAPS.items():
     total = 0
     for c in caps:
