@@ -5,7 +5,7 @@
 // triangular-weighted average of downsample_kernel_gpu.cu.cc:35-76, and every scale is
 // computed DIRECTLY from the input (the scale centres are not nested, so no scale can be derived from another).
 //
-// Work split: a thread-block cluster of up to 8 CTAs owns one image; rank r walks the input rows
+// Work split: a thread-block cluster of up to 16 CTAs (8 once the batch fills the chip) owns one image; rank r walks the input rows
 // [r*chunk, (r+1)*chunk).  Thread x owns PX adjacent input columns and reads each of its rows exactly once (coalesced
 // 16-byte loads, U rows in flight).  The weight is separable, w = wx(x) * wy(y): an input row feeds at most two output
 // rows of every scale (the last centre at or above it, and the next one), so the thread keeps, per scale, the vertical
@@ -15,6 +15,7 @@
 // into the rank's partial-result table.  After the walk the ranks add their partial rows through distributed shared
 // memory in rank order (deterministic) and apply the NaN rule (:72-76).  Every input byte is read once from DRAM;
 // all scales together write < 2 % of that.
+#include <cstdlib>
 #include <cooperative_groups.h>
 #include <mutex>
 #include "fn2_common.cuh"
@@ -27,7 +28,7 @@ namespace cg = cooperative_groups;
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MS = 5;          // scales per launch (the reference's losses use five, flownet_c.py:135-160)
-constexpr int MAX_RANKS = 8;   // portable cluster size
+constexpr int MAX_RANKS = 16;  // largest cluster (non-portable size, opted into per kernel); 8 is the portable fallback
 
 struct MsParams {
   int N, iH, iW, ns, chunk;
@@ -46,6 +47,13 @@ __host__ __device__ inline size_t ms_smem_words(int chunk, int ncols, int nv, in
          + (size_t)nv * ncols                // parked row
          + ptTotal;                          // partial results
 }
+
+#ifdef FN2_TIMELINE
+__device__ long long g_tld[16];
+#define TLD(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tld[i] = clock64(); } while (0)
+#else
+#define TLD(i) do {} while (0)
+#endif
 
 template <int CT, int PX, int U>
 __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const float* __restrict__ in) {
@@ -73,6 +81,7 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
   float* rowbuf = totRow + p.trTotal;                      // [NV][ncols] the parked output row
   float* part = rowbuf + (size_t)NV * ncols;               // per scale [maxRows][oW][NV + 1]
 
+  TLD(0);
   // ---- tables ----
   for (int idx = tid; idx < MS * chunk; idx += nthr) {
     const int s = idx / chunk, i = idx - s * chunk, y = yb + i;
@@ -116,8 +125,10 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
       for (int s = 0; s < p.ns; ++s) m |= (rowD[s * chunk + i] != rowD[s * chunk + i - 1]) ? (1 << s) : 0;
     fmask[i] = m;
   }
-  for (int s = 0; s < p.ns; ++s)
-    for (int dyl = tid; dyl < p.maxRows[s]; dyl += nthr) {
+  for (int idx = tid; idx < p.trTotal; idx += nthr) {   // every (scale, local output row) on its own thread
+      int s = 0;
+      while (s + 1 < p.ns && p.trOff[s + 1] <= idx) ++s;
+      const int dyl = idx - p.trOff[s];
       const int dy = dF[rank][s] + dyl;
       float t = 0.f;
       for (int i = 0; i <= ye - yb; ++i) {
@@ -129,6 +140,7 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
     }
   __syncthreads();
 
+  TLD(1);
   // ---- horizontal pass of the parked row -> partial-result row dy of scale s ----
   auto horizontal = [&](int s, int dy) {
     __syncthreads();                                       // the parked row is complete
@@ -256,6 +268,7 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
       }
     }
   }
+  TLD(2);
   if (yb <= ye) {
 #pragma unroll
     for (int s = 0; s < MS; ++s)
@@ -275,8 +288,10 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
       }
   }
 
+  TLD(3);
   // ---- combine the ranks' partial rows in rank order and finish (:72-76) ----
   cluster.sync();
+  TLD(4);
   for (int s = 0; s < p.ns; ++s) {
     const int oW = p.oW[s];
     const int total = p.oH[s] * oW * CT;
@@ -294,7 +309,9 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
       o[idx] = (n_ / w_ > 0.5f) ? nan_f() : v_ / w_;
     }
   }
+  TLD(5);
   cluster.sync();   // keep this CTA's shared memory alive until every rank has read it
+  TLD(6);
 }
 
 template <int CT, int PX, int U>
@@ -304,6 +321,7 @@ int launch_multi(const MsParams& p, int rs, int nthr, const float* in, cudaStrea
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
     attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
   cudaLaunchConfig_t cfg = {};
@@ -319,20 +337,25 @@ int launch_multi(const MsParams& p, int rs, int nthr, const float* in, cudaStrea
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p, in);
-  if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    if (rs > 8) return 2;   // a 16-CTA cluster does not fit this device / partition: the caller retries with 8
+    note_cuda_error(e);
+    return FN2_E_CUDA;
+  }
   return after_launch();
 }
 
 // One fused launch for up to MS scales; returns 1 if this group of scales cannot take the fused kernel.
 int try_fused(const float* in, float* const* outs, const int* out_hw, int ns, int N, int iH, int iW, int C,
-              cudaStream_t st) {
+              cudaStream_t st, int max_ranks) {
   if (C != 1 && C != 2) return 1;
   const int px = C == 1 ? (iW % 4 == 0 ? 4 : 1) : (iW % 2 == 0 ? 2 : 1);
   const int nthr = (((iW + px - 1) / px + 31) / 32) * 32;
   if (nthr > 512 || iW < px) return 1;
   if ((long long)N * MAX_RANKS > 0x7fffffffLL) return 1;
   int rs = 1;
-  while (rs < MAX_RANKS && iH >= 32 * rs) rs *= 2;          // >= 16 rows per rank
+  while (rs < max_ranks && iH >= 32 * rs) rs *= 2;          // >= 16 rows per rank
   MsParams p = {};
   p.N = N; p.iH = iH; p.iW = iW; p.ns = ns;
   p.chunk = (iH + rs - 1) / rs;
@@ -358,11 +381,31 @@ int try_fused(const float* in, float* const* outs, const int* out_hw, int ns, in
 
 }  // namespace
 
+#ifdef FN2_TIMELINE
+extern "C" __attribute__((visibility("default"))) int fn2_debug_timeline_ds(long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_tld, sizeof(long long) * 16);
+}
+#endif
+
 int downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
                              int iW, int C, cudaStream_t st) {
   for (int s0 = 0; s0 < num_scales; s0 += MS) {
     const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
-    int rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st);
+    // 16-CTA clusters only while they leave SMs free (measured on B200: N=8 0.080 -> 0.067 ms, but N=32 0.107 ->
+    // 0.212 ms: 16 co-scheduled CTAs per GPC serialise once the chip is full)
+    static int big_ok = 1, sms = 0;
+    if (sms == 0) {
+      int dev = 0, v = 0;
+      if (cudaGetDevice(&dev) == cudaSuccess) (void)cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+      sms = v > 0 ? v : 148;
+    }
+    int max_ranks = (big_ok && (long long)N * MAX_RANKS <= sms) ? MAX_RANKS : 8;
+    if (const char* e = getenv("FN2_DS_MAX_RANKS")) max_ranks = atoi(e);
+    int rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, max_ranks);
+    if (rc == 2) {   // no room for 16-CTA clusters here: stay with the portable size from now on
+      big_ok = 0;
+      rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, 8);
+    }
     if (rc == 1) {   // shapes the fused kernel does not take: one single-scale launch per size (downsample.cu)
       for (int s = s0; s < s0 + ns; ++s) {
         rc = downsample_forward(in, outs[s], N, iH, iW, C, out_hw[2 * s], out_hw[2 * s + 1], st);
