@@ -400,7 +400,7 @@ int downsample_multi_forward(const float* in, float* const* outs, const int* out
       sms = v > 0 ? v : 148;
     }
     int max_ranks = (big_ok && (long long)N * MAX_RANKS <= sms) ? MAX_RANKS : 8;
-    if (const char* e = getenv("FN2_DS_MAX_RANKS")) max_ranks = atoi(e);
+    if (const char* e = getenv("FN2_DS_MAX_RANKS")) max_ranks = min(max(atoi(e), 1), MAX_RANKS);   // A/B switch
     int rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, max_ranks);
     if (rc == 2) {   // no room for 16-CTA clusters here: stay with the portable size from now on
       big_ok = 0;
