@@ -33,6 +33,26 @@ def test_loss_scales_match_oracle(C):
         assert_close(got.cpu().numpy(), want, rel=1e-5, abs_=5e-6, what="multi %s C=%d" % (size, C))
 
 
+@pytest.mark.parametrize("ranks", [8, 16])
+def test_both_cluster_sizes_match_oracle(ranks, monkeypatch):
+    """Small batches take 16-CTA clusters, batches that fill the chip 8 (downsample_multi.cu); the developer switch
+    forces either, so both row partitions are checked at the loss shape whatever the batch."""
+    monkeypatch.setenv("FN2_DS_MAX_RANKS", str(ranks))
+    x = _input(2, 384, 512, 2, 4321)
+    outs = fn2.downsample_multi(x.cuda(), LOSS_SIZES)
+    for size, got in zip(LOSS_SIZES, outs):
+        assert_close(got.cpu().numpy(), o.c_downsample(x.numpy(), size), rel=1e-5, abs_=5e-6,
+                     what="ranks %d %s" % (ranks, size))
+
+
+def test_large_batch_takes_the_portable_cluster_size():
+    """N x 16 > SM count: the launch falls back to 8 ranks per image; same numbers as the oracle."""
+    x = _input(12, 384, 512, 2, 99, nan=False)
+    outs = fn2.downsample_multi(x.cuda(), LOSS_SIZES[:2])
+    for size, got in zip(LOSS_SIZES[:2], outs):
+        assert_close(got.cpu().numpy(), o.c_downsample(x.numpy(), size), rel=1e-5, abs_=5e-6, what="N=12 %s" % (size,))
+
+
 @pytest.mark.parametrize("shape,sizes", [
     ((3, 48, 64, 2), [(3, 4), (6, 8), (12, 16)]),            # two cluster ranks
     ((1, 100, 130, 2), [(7, 9), (13, 33), (50, 40)]),         # ragged: rows not divisible by the ranks, odd widths
