@@ -391,15 +391,16 @@ int downsample_multi_forward(const float* in, float* const* outs, const int* out
                              int iW, int C, cudaStream_t st) {
   for (int s0 = 0; s0 < num_scales; s0 += MS) {
     const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
-    // 16-CTA clusters only while they leave SMs free (measured on B200: N=8 0.080 -> 0.067 ms, but N=32 0.107 ->
-    // 0.212 ms: 16 co-scheduled CTAs per GPC serialise once the chip is full)
+    // 16-CTA clusters only up to ~1.3 CTAs per SM (measured on B200, 8 -> 16 ranks: N=4 0.079 -> 0.057 ms, N=12
+    // 0.088 -> 0.067, but N=16 0.103 -> 0.134 and N=32 0.107 -> 0.212: 16 co-scheduled CTAs per GPC serialise once
+    // the chip is full)
     static int big_ok = 1, sms = 0;
     if (sms == 0) {
       int dev = 0, v = 0;
       if (cudaGetDevice(&dev) == cudaSuccess) (void)cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
       sms = v > 0 ? v : 148;
     }
-    int max_ranks = (big_ok && (long long)N * MAX_RANKS <= sms) ? MAX_RANKS : 8;
+    int max_ranks = (big_ok && (long long)N * MAX_RANKS * 10 <= (long long)sms * 13) ? MAX_RANKS : 8;
     if (const char* e = getenv("FN2_DS_MAX_RANKS")) max_ranks = min(max(atoi(e), 1), MAX_RANKS);   // A/B switch
     int rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, max_ranks);
     if (rc == 2) {   // no room for 16-CTA clusters here: stay with the portable size from now on
