@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfn2ops.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
-PRECISIONS = {"fp32": 0, "tf32": 1, "bf16": 2, "tf32x3": 3}
+PRECISIONS = {"fp32": 0, "tf32": 1, "tf32x3": 3}
 
 _lock = threading.Lock()
 _lib = None
@@ -28,6 +28,7 @@ _SIGNATURES = {
     "fn2_last_cuda_error": (c_int, []),
     "fn2_launch_count": (ctypes.c_ulonglong, []),
     "fn2_correlation_output_shape": (c_int, [c_int] * 7 + [ctypes.POINTER(c_int)] * 3),
+    "fn2_correlation_precision_supported": (c_int, _CORR_GEOM + [c_int]),
     "fn2_correlation_workspace_bytes": (c_size_t, _CORR_GEOM + [c_int, c_int]),
     "fn2_correlation_forward": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_forward_fused": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, ctypes.c_float, c_int, c_void_p,

@@ -6,21 +6,40 @@ float32 CUDA tensors.  Shape and error behaviour follow ``src/ops/correlation/co
 """
 import ctypes
 import os
+import warnings
 
 import torch
 
 from . import _lib
 
-#: arithmetic of the contraction when the caller does not pass ``precision=``: "fp32" (default; matches the
-#: reference within 1e-5 rel / 1e-6 abs), "tf32", "bf16" or "tf32x3".  Override with FN2_CORR_PRECISION.
-DEFAULT_PRECISION = os.environ.get("FN2_CORR_PRECISION", "fp32")
+#: Arithmetic of the contraction when the caller does not pass ``precision=``.  "auto" (default) is the fastest mode
+#: that meets the reference's float32 tolerance (1e-5 rel / 1e-6 abs): "tf32x3" (split-tf32 on the tensor cores) where
+#: the call has the FlowNetC shape, else "fp32" (CUDA cores, any geometry).  "tf32" is faster and less accurate
+#: (2.5e-3 of the tensor's maximum).  Override with FN2_CORR_PRECISION.
+DEFAULT_PRECISION = os.environ.get("FN2_CORR_PRECISION", "auto")
+
+_NAMES = {v: n for n, v in _lib.PRECISIONS.items()}
 
 
-def _prec(precision):
+def _prec(precision, geom):
+    """Resolve ``precision`` for one call (geom = N,H,W,C,k,md,s1,s2,pad) to the ABI's enum value.  A tensor-core
+    mode asked for on a geometry it does not cover falls back to "fp32" with a warning (never to less accuracy)."""
     p = DEFAULT_PRECISION if precision is None else precision
-    if p not in _lib.PRECISIONS:
-        raise ValueError("precision must be one of %s" % sorted(_lib.PRECISIONS))
-    return _lib.PRECISIONS[p]
+    if p != "auto" and p not in _lib.PRECISIONS:
+        raise ValueError("precision must be 'auto' or one of %s" % sorted(_lib.PRECISIONS))
+    want = _lib.PRECISIONS["tf32x3" if p == "auto" else p]
+    if want == 0:
+        return 0
+    ok = _lib.lib().fn2_correlation_precision_supported(*geom, want)
+    if ok < 0:
+        _lib.check(ok, "Correlation")
+    if ok == 1:
+        return want
+    if p != "auto":
+        warnings.warn("correlation: precision=%r does not cover this call (needs kernel_size 1, stride_1 1, "
+                      "pad == max_displacement, max_displacement // stride_2 == 10, C %% 32 == 0, C <= 256); "
+                      "using the fp32 CUDA-core kernels" % p, RuntimeWarning, stacklevel=3)
+    return 0
 
 
 def output_shape(H, W, kernel_size, max_displacement, stride_1, stride_2, padding):
@@ -67,10 +86,11 @@ def _forward(a, b, k, md, s1, s2, pad, prec):
 def correlation_grad(gradients, input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, pad,
                      precision=None):
     """The ``CorrelationGrad`` op (correlation_op.cc:64-82): returns (backprops_a, backprops_b)."""
-    prec = _prec(precision)
     _check_pair(input_a, input_b)
     _lib.require_cuda_f32(gradients, "gradients")
     N, H, W, C = input_a.shape
+    prec = precision if isinstance(precision, int) else _prec(
+        precision, (N, H, W, C, kernel_size, max_displacement, stride_1, stride_2, pad))
     oh, ow, oc = output_shape(H, W, kernel_size, max_displacement, stride_1, stride_2, pad)
     if tuple(gradients.shape) != (N, oh, ow, oc):
         raise ValueError("gradients must have shape %s, got %s" % ((N, oh, ow, oc), tuple(gradients.shape)))
@@ -97,18 +117,19 @@ class _Correlation(torch.autograd.Function):
     def backward(ctx, gradients):
         a, b = ctx.saved_tensors
         k, md, s1, s2, pad, prec = ctx.attrs
-        names = {v: n for n, v in _lib.PRECISIONS.items()}
-        ga, gb = correlation_grad(gradients.contiguous(), a, b, k, md, s1, s2, pad, precision=names[prec])
+        ga, gb = correlation_grad(gradients.contiguous(), a, b, k, md, s1, s2, pad, precision=prec)
         return ga, gb, None, None, None, None, None, None
 
 
 def correlation(input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, padding, *, precision=None):
     """Cost volume between two feature maps; same positional signature as the reference wrapper.
 
-    ``precision`` is the one keyword-only extension: "fp32" (default), "tf32", "bf16", "tf32x3".
+    ``precision`` is the one keyword-only extension: "auto" (default: "tf32x3" where the tensor-core kernels cover the
+    call, else "fp32" -- both meet the reference's float32 tolerance), "fp32", "tf32x3" or "tf32".
     """
     args = [int(v) for v in (kernel_size, max_displacement, stride_1, stride_2, padding)]
-    return _Correlation.apply(input_a, input_b, *args, _prec(precision))
+    _check_pair(input_a, input_b)
+    return _Correlation.apply(input_a, input_b, *args, _prec(precision, tuple(input_a.shape) + tuple(args)))
 
 
 # ---- fused forward epilogue (SURVEY.md section 8 f-2) ----------------------------------------------------------
@@ -147,8 +168,7 @@ class _CorrelationLeakyConcat(torch.autograd.Function):
         offset, oc, slope, k, md, s1, s2, pad, prec = ctx.attrs
         cc = buf[..., offset:offset + oc]
         g = (gbuf[..., offset:offset + oc] * torch.where(cc > 0, 1.0, float(slope))).contiguous()
-        names = {v: n for n, v in _lib.PRECISIONS.items()}
-        ga, gb = correlation_grad(g, a, b, k, md, s1, s2, pad, precision=names[prec])
+        ga, gb = correlation_grad(g, a, b, k, md, s1, s2, pad, precision=prec)
         gbuf = gbuf.clone()
         gbuf[..., offset:offset + oc] = 0
         return ga, gb, gbuf, None, None, None, None, None, None, None, None
@@ -161,5 +181,8 @@ def correlation_leaky_concat(input_a, input_b, kernel_size, max_displacement, st
     tf.concat) -- the [N,h,w,441] volume makes no round trip through HBM.  ``buf`` is a contiguous NHWC float32
     tensor whose other channels (conv_redir's 32) the caller fills, before or after."""
     args = [int(v) for v in (kernel_size, max_displacement, stride_1, stride_2, padding)]
+    _check_pair(input_a, input_b)
+    if not float(leaky_slope) > 0:   # the backward reads the mask off the sign of the stored output
+        raise ValueError("leaky_slope must be > 0, got %r" % (leaky_slope,))
     return _CorrelationLeakyConcat.apply(input_a, input_b, buf, int(channel_offset), float(leaky_slope), *args,
-                                         _prec(precision))
+                                         _prec(precision, tuple(input_a.shape) + tuple(args)))

@@ -2,7 +2,7 @@
 //
 // These kernels cover the whole parameter space of the reference op (correlation_kernel.cu.cc:21-119,
 // correlation_grad_kernel.cu.cc:20-189); the FlowNetC call (k=1, s1=1) is served by the tiled kernels in
-// corr_simt.cu / corr_tc.cu.  Zero padding is a bounds test on the un-padded tensors: no padded temporaries,
+// corr_tc.cu / corr_tc_x3.cu.  Zero padding is a bounds test on the un-padded tensors: no padded temporaries,
 // no memset (the reference's Pad, pad.cu.cc:14-74, is gone).  One launch covers the whole batch.
 #include "fn2_common.cuh"
 

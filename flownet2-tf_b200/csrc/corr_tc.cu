@@ -564,7 +564,7 @@ size_t fwd_smem_bytes(int nkc) {
 }  // namespace
 
 bool corr_tc_supported(const CorrGeom& g, int precision) {
-  if (precision != FN2_PREC_TF32) return false;
+  if (precision != FN2_PREC_TF32 && precision != FN2_PREC_TF32X3) return false;
   if (g.k != 1 || g.s1 != 1 || g.pad != g.md) return false;
   if (g.s2 != 1 && g.s2 != 2) return false;
   if (g.r != 10) return false;                       // window radius instantiated below
@@ -578,6 +578,7 @@ size_t corr_tc_workspace_bytes(const CorrGeom&, int, int) { return 0; }
 int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void*, size_t,
                     cudaStream_t st) {
   if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  if (precision == FN2_PREC_TF32X3) return corr_tc_x3_forward(g, a, b, out, st);   // corr_tc_x3.cu
   TcParams P;
   P.out = out;
   P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
@@ -607,36 +608,32 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
   }
   for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; P.b2[cls] = P.b2[0]; }
   const size_t smem = fwd_smem_bytes(P.nkc);
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)fwd_smem_bytes(MAX_KC));
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)fwd_smem_bytes(MAX_KC));
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(corr_tc_fwd_pair_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)fwd_pair_smem_bytes(MAX_KC));
+  static PerDeviceOnce once;   // function attributes are per device
+  const cudaError_t attr_err = per_device_once(once, [] {
+    cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)fwd_smem_bytes(MAX_KC));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_fwd_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)fwd_smem_bytes(MAX_KC));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_fwd_pair_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)fwd_pair_smem_bytes(MAX_KC));
+    return e;
   });
-  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
-  if (P.TX == 1 && !getenv("FN2_NO_PAIR")) {   // narrow images: CTA pairs share every b block
+  const EnvSwitches& sw = env_switches();
+  if (P.TX == 1 && !sw.no_pair) {   // narrow images: CTA pairs share every b block
     // Tail split: with `slots` CTA pairs resident at a time, the last npairs % slots pair tiles would run alone in
     // a final wave; cut each into pieces of g blocks (smallest g whose pieces all fit in that wave).
-    static int slots = 0;
-    if (slots == 0) {
-      int dev = 0, sms = 148;
-      if (cudaGetDevice(&dev) == cudaSuccess) (void)cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      slots = sms / 2 > 0 ? sms / 2 : 1;
-    }
+    const int slots = std::max(device_sm_count() / 2, 1);
     const long long npairs = (long long)g.N * P.ncls * P.TYP;
     const int rows_max = std::min(P.Hcb[0], 2 * TILE_R + 2 * 10);
     const int maxblk = (rows_max + 3) / 4;
     const int tail_tiles = (int)(npairs % slots);
     P.n_full = (int)npairs; P.split_units = 1; P.split_g = maxblk;
-    if (npairs > slots && tail_tiles > 0 && !getenv("FN2_NO_SPLIT")) {
+    if (npairs > slots && tail_tiles > 0 && !sw.no_split) {
       for (int gsz = 1; gsz < maxblk; ++gsz) {
         const int units = (maxblk + gsz - 1) / gsz;
         if ((long long)tail_tiles * units <= slots) {
@@ -649,7 +646,7 @@ int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* ou
     if (nwork > 0x3fffffffLL) return FN2_E_BAD_SHAPE;
     P.nwork = (int)nwork;
     // persistent: one pair per pair of SMs strides over the work list (FN2_NO_PERSIST: one pair per unit of work)
-    const long long pgrid = 2 * (getenv("FN2_NO_PERSIST") ? nwork : std::min<long long>(nwork, slots));
+    const long long pgrid = 2 * (sw.no_persist ? nwork : std::min<long long>(nwork, slots));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)pgrid);
     cfg.blockDim = dim3(NTHREADS);
@@ -684,7 +681,6 @@ int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const
   if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
   if (corr_tc_bwd_supported(g, precision)) return corr_tc_backward_launch(g, gout, a, b, ga, gb, precision, st);
   // shapes the tensor-core backward does not cover: the fp32 CUDA-core path keeps the op differentiable
-  if (corr_simt_supported(g)) return corr_simt_backward(g, gout, a, b, ga, gb, st);
   return corr_generic_backward(g, gout, a, b, ga, gb, st);
 }
 

@@ -29,6 +29,14 @@
 //
 // Warp roles (576 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-17 = G builders, then
 // epilogue.
+//
+// fp32-grade mode (X3, FN2_PREC_TF32X3): both operands are split as x = hi + lo (hi = the 19 bits the tensor core
+// reads from a raw fp32 word, lo = x - hi; fn2_tc.cuh x3_lo) and every step issues THREE MMAs into the same
+// accumulator: X.G + X_lo.G + X.G_lo (the lo.lo term, ~2^-21 relative, is dropped).  The builders write G_lo next to
+// G from the value they already hold in a register, and convert the TMA-landed X chunk to X_lo in shared memory.  To
+// make room a CTA takes only 128 of the channels (grid x ceil(C/128)): a stage is X 16 KB + X_lo 16 KB + G 32 KB +
+// G_lo 32 KB, two stages, and the accumulator needs 256 TMEM columns.  Results meet the fp32 tolerance
+// (1e-5 relative + 1e-6 absolute against a float64 evaluation).
 #include <type_traits>
 #include "fn2_tc.cuh"
 
@@ -74,27 +82,34 @@ struct __align__(8) BwdBarriers {
   uint32_t tmem_base;
 };
 
-template <int NST>
+template <int NST, bool X3>
 constexpr size_t bwd_smem_bytes() {
-  return 1024 + (size_t)NST * (XSTAGE + GSTAGE) + sizeof(BwdBarriers<NST>);
+  return 1024 + (size_t)NST * (XSTAGE + (X3 ? 2 : 1) * GSTAGE) + sizeof(BwdBarriers<NST>);
 }
 
-template <int NST, int S2, int R>
+template <int NST, int S2, int R, bool X3>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
-  static_assert(NST == 3 || NST == 4, "the G builders unroll the stage ring explicitly");
+  static_assert(NST >= 2 && NST <= 4, "the G builders unroll the stage ring explicitly");
   constexpr int GW = 2 * R + 1;
   constexpr int D = GW * GW;
+  // X3: the X stage holds 4 raw chunks (this CTA's 128 channels) then their 4 lo chunks -- the same 32 KB, addressed
+  // like the two channel halves of the plain kernel; the G stage holds G then G_lo.
+  constexpr int GST = X3 ? 2 * GSTAGE : GSTAGE;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sX = smem;
   uint8_t* sG = sX + (size_t)NST * XSTAGE;
-  BwdBarriers<NST>* bars = reinterpret_cast<BwdBarriers<NST>*>(sG + (size_t)NST * GSTAGE);
+  BwdBarriers<NST>* bars = reinterpret_cast<BwdBarriers<NST>*>(sG + (size_t)NST * GST);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // ---- which tile: (((n * ncls + cls) * TY + ty) * TX + tx) * 2 + mode ----
+  // ---- which tile: ((((n * ncls + cls) * TY + ty) * TX + tx) * nhalf + ch) * 2 + mode   (ch: X3 only) ----
   int t = blockIdx.x;
   const int mode = t & 1; t >>= 1;
+  int ch = 0;                                     // X3: which 128 channels this CTA produces
+  if (X3) { ch = t % P.nhalf; t /= P.nhalf; }
+  const int c_first = ch * 4;                     // first 32-channel chunk
+  const int nch_x = X3 ? min(4, P.nchunk - c_first) : P.nchunk;   // chunks this CTA streams
   const int tx = t % P.TX; t /= P.TX;
   const int ty = t % P.TY; t /= P.TY;
   const int cls = t % P.ncls;
@@ -122,7 +137,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
       const int row = r0 + qq;
       if (row >= Hout) break;
       float* orow = outp + (((size_t)n * Hfull + (size_t)(row * P.s2 + cy)) * P.W + cx + (size_t)x0 * P.s2) * P.C;
-      for (int e = threadIdx.x; e < ncol * P.C; e += NTHREADS) orow[(size_t)(e / P.C) * P.s2 * P.C + e % P.C] = 0.f;
+      if (X3) {   // this CTA's channels only
+        const int cw = nch_x * KCH;
+        for (int e = threadIdx.x; e < ncol * cw; e += NTHREADS)
+          orow[(size_t)(e / cw) * P.s2 * P.C + c_first * KCH + e % cw] = 0.f;
+      } else {
+        for (int e = threadIdx.x; e < ncol * P.C; e += NTHREADS) orow[(size_t)(e / P.C) * P.s2 * P.C + e % P.C] = 0.f;
+      }
     }
     return;
   }
@@ -137,7 +158,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), TMEM_COLS);
+  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), X3 ? TILE_N : TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -153,9 +174,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
         const int xs0 = nhx > 1 ? x0 - 16 + 32 * (it % nhx) : 0;
         mbar_wait(smem_u32(&bars->empty[stage]), ((it / NST) & 1) ^ 1);
         const uint32_t full = smem_u32(&bars->x_full[stage]);
-        mbar_expect_tx(full, (uint32_t)nchunk * XCHUNK);
-        for (int c = 0; c < nchunk; ++c)
-          tma_load_4d(smem_u32(sX + (size_t)stage * XSTAGE + (size_t)c * XCHUNK), map, full, c * KCH, xs0, row, n);
+        mbar_expect_tx(full, (uint32_t)nch_x * XCHUNK);
+        for (int c = 0; c < nch_x; ++c)
+          tma_load_4d(smem_u32(sX + (size_t)stage * XSTAGE + (size_t)c * XCHUNK), map, full, (c_first + c) * KCH, xs0,
+                      row, n);
       }
     }
   } else if (warp == 1) {
@@ -172,14 +194,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
         mbar_wait(smem_u32(&bars->g_full[stage]), par);
         tc_fence_after();
         const uint32_t x_addr = smem_u32(sX + (size_t)stage * XSTAGE);
-        const uint32_t g_addr = smem_u32(sG + (size_t)stage * GSTAGE);
-        for (int h = 0; h < P.nhalf; ++h) {
+        const uint32_t g_addr = smem_u32(sG + (size_t)stage * GST);
+        if constexpr (X3) {
 #pragma unroll
           for (int k8 = 0; k8 < 4; ++k8) {
-            const uint64_t adesc = desc_sw128b32_mnmajor(x_addr + h * 4 * XCHUNK + k8 * 1024, XCHUNK, 512);
-            const uint64_t bdesc = mode ? desc_sw128b32_mnmajor(g_addr + k8 * 1024, GBLOCK, 512)
-                                        : desc_sw128_kmajor(g_addr + k8 * 32);
-            umma_tf32(tmem_base + (uint32_t)h * TILE_N, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
+            const uint64_t a_hi = desc_sw128b32_mnmajor(x_addr + k8 * 1024, XCHUNK, 512);
+            const uint64_t a_lo = desc_sw128b32_mnmajor(x_addr + 4 * XCHUNK + k8 * 1024, XCHUNK, 512);
+            const uint64_t b_hi = mode ? desc_sw128b32_mnmajor(g_addr + k8 * 1024, GBLOCK, 512)
+                                       : desc_sw128_kmajor(g_addr + k8 * 32);
+            const uint64_t b_lo = mode ? desc_sw128b32_mnmajor(g_addr + GSTAGE + k8 * 1024, GBLOCK, 512)
+                                       : desc_sw128_kmajor(g_addr + GSTAGE + k8 * 32);
+            umma_tf32(tmem_base, a_lo, b_hi, idesc, (uint32_t)((it | k8) != 0));   // small terms first
+            umma_tf32(tmem_base, a_hi, b_lo, idesc, 1u);
+            umma_tf32(tmem_base, a_hi, b_hi, idesc, 1u);
+          }
+        } else {
+          for (int h = 0; h < P.nhalf; ++h) {
+#pragma unroll
+            for (int k8 = 0; k8 < 4; ++k8) {
+              const uint64_t adesc = desc_sw128b32_mnmajor(x_addr + h * 4 * XCHUNK + k8 * 1024, XCHUNK, 512);
+              const uint64_t bdesc = mode ? desc_sw128b32_mnmajor(g_addr + k8 * 1024, GBLOCK, 512)
+                                          : desc_sw128_kmajor(g_addr + k8 * 32);
+              umma_tf32(tmem_base + (uint32_t)h * TILE_N, adesc, bdesc, idesc, (uint32_t)((it | k8) != 0));
+            }
           }
         }
         umma_commit(smem_u32(&bars->empty[stage]));  // frees X and G of this stage once the MMAs have read them
@@ -255,7 +292,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
             mbar_wait(smem_u32(&bars->empty[st]), par);
 #pragma unroll
             for (int rr = 0; rr < 16; ++rr)
-              asm volatile("st.shared.f32 [%0+%2], %1;" ::"r"(saddr[rr]), "f"(cur[rr]), "n"(st * GSTAGE) : "memory");
+              asm volatile("st.shared.f32 [%0+%2], %1;" ::"r"(saddr[rr]), "f"(cur[rr]), "n"(st * GST) : "memory");
+            if constexpr (X3) {
+#pragma unroll
+              for (int rr = 0; rr < 16; ++rr)
+                asm volatile("st.shared.f32 [%0+%2], %1;" ::"r"(saddr[rr]), "f"(x3_lo(cur[rr])), "n"(st * GST + GSTAGE)
+                             : "memory");
+              // X_lo from the raw X chunks TMA has landed for this item: 16 KB, two float4 per builder thread
+              mbar_wait(smem_u32(&bars->x_full[st]), par ^ 1);
+              uint8_t* xs = sX + (size_t)st * XSTAGE;
+              const int o0 = (int)(threadIdx.x - 64) * 16;
+              const float4 x0v = *reinterpret_cast<const float4*>(xs + o0);
+              const float4 x1v = *reinterpret_cast<const float4*>(xs + o0 + NBUILD * 32 * 16);
+              *reinterpret_cast<float4*>(xs + 4 * XCHUNK + o0) = x3_lo4(x0v);
+              *reinterpret_cast<float4*>(xs + 4 * XCHUNK + o0 + NBUILD * 32 * 16) = x3_lo4(x1v);
+            }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA
             __syncwarp();
             if (lane == 0) mbar_arrive(smem_u32(&bars->g_full[st]));
@@ -263,7 +314,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
         };
         stage_body(std::integral_constant<int, 0>{});
         stage_body(std::integral_constant<int, 1>{});
-        stage_body(std::integral_constant<int, 2>{});
+        if constexpr (NST >= 3) stage_body(std::integral_constant<int, 2>{});
         if constexpr (NST == 4) stage_body(std::integral_constant<int, 3>{});
       }
     }
@@ -281,8 +332,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     const uint32_t stg = smem_u32(sX) + (uint32_t)bw * 8192u;
     const CUtensorMap* omap = &P.o[mode][cls];
     int nb = 0;
-    for (int h = 0; h < P.nhalf; ++h) {
-      const int c0 = h * 128 + qd * 32;
+    for (int h = 0; h < (X3 ? 1 : P.nhalf); ++h) {
+      const int c0 = (X3 ? ch : h) * 128 + qd * 32;
       if (c0 >= P.C) break;         // warp-uniform
       for (int qq = e; qq < TILE_R; qq += NBUILD / 4) {
         const int row = r0 + qq;
@@ -314,16 +365,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    tmem_dealloc(tmem_base, X3 ? TILE_N : TMEM_COLS);
   }
 }
 
 constexpr int BWD_NST = 3;
+constexpr int BWD_NST_X3 = 2;
 
 }  // namespace
 
 bool corr_tc_bwd_supported(const CorrGeom& g, int precision) {
-  if (precision != FN2_PREC_TF32) return false;
+  if (precision != FN2_PREC_TF32 && precision != FN2_PREC_TF32X3) return false;
   if (g.k != 1 || g.s1 != 1 || g.pad != g.md) return false;
   if (g.s2 != 1 && g.s2 != 2) return false;
   if (g.C % KCH != 0 || g.C / KCH > MAX_CH) return false;
@@ -335,6 +387,7 @@ bool corr_tc_bwd_supported(const CorrGeom& g, int precision) {
 int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
                             int precision, cudaStream_t st) {
   if (!corr_tc_bwd_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
+  const bool x3 = precision == FN2_PREC_TF32X3;
   BwdParams P;
   P.grad = gout;
   P.out[0] = ga; P.out[1] = gb;
@@ -373,19 +426,27 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
         return FN2_E_CUDA;
     }
   }
-  auto kern = g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST, 2, 10> : corr_tc_bwd_kernel<BWD_NST, 1, 10>;
-  constexpr size_t smem = bwd_smem_bytes<BWD_NST>();
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 2, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)smem);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 1, 10>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  auto kern = x3 ? (g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true> : corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true>)
+                 : (g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST, 2, 10, false> : corr_tc_bwd_kernel<BWD_NST, 1, 10, false>);
+  const size_t smem = x3 ? bwd_smem_bytes<BWD_NST_X3, true>() : bwd_smem_bytes<BWD_NST, false>();
+  static PerDeviceOnce once;   // function attributes are per device
+  const cudaError_t attr_err = per_device_once(once, [] {
+    cudaError_t e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 2, 10, false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)bwd_smem_bytes<BWD_NST, false>());
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 1, 10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)bwd_smem_bytes<BWD_NST, false>());
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)bwd_smem_bytes<BWD_NST_X3, true>());
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)bwd_smem_bytes<BWD_NST_X3, true>());
+    return e;
   });
-  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
-  const long long grid = (long long)g.N * P.ncls * P.TY * P.TX * 2;
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  const long long grid = (long long)g.N * P.ncls * P.TY * P.TX * 2 * (x3 ? P.nhalf : 1);
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   kern<<<(unsigned)grid, NTHREADS, smem, st>>>(P);
   return after_launch();

@@ -1,0 +1,397 @@
+// corr_tc_x3.cu -- FlowNetC correlation FORWARD at fp32-grade accuracy on the tensor cores (split-TF32), sm_100a.
+//
+// The reference op is fp32 end to end (correlation_op.cc:54-61, arithmetic correlation_kernel.cu.cc:72-110).  A single
+// kind::tf32 MMA keeps 11 significant bits of each operand; here every fp32 operand x is split into hi = its top 19
+// bits (what the tensor core reads from the raw fp32 word anyway) and lo = x - hi (exact, rounded to 11 bits, see
+// fn2_tc.cuh x3_lo), and the products hi*hi, hi*lo, lo*hi and lo*lo are all accumulated in fp32:
+//   <a, b> = <a_hi, b_hi> + <a_hi, b_lo> + <a_lo, b_hi> + <a_lo, b_lo>        error ~2^-21 per product
+// Same banded-Gram formulation as corr_tc.cu (parity classes, 4 b-rows x 32 b-columns per block, TMA zero fill as the
+// op's padding), with the split folded into the MMA shape instead of into extra instructions:
+//   * one CTA owns 64 a-pixels (2 class-rows x 32 class-cols).  Its A operand has M = 128 rows: rows 0..63 the raw
+//     pixels, rows 64..127 their lo parts, resident in shared memory for the full K = C (128 KB at C = 256).
+//   * every streamed block of 128 b-pixels becomes N = 256 operand rows: 128 raw + 128 lo.  ONE tcgen05.mma
+//     M128 N256 K8 therefore produces all four partial products at the full-rate shape; they land in four quadrants
+//     of the [128 x 256] accumulator:  lanes 0..63 x cols 0..127 = hi*hi, x cols 128..255 = hi*lo,
+//                                       lanes 64..127 x cols 0..127 = lo*hi, x cols 128..255 = lo*lo.
+//   * lo parts are made in shared memory by four converter warps (raw chunk -> lo chunk at the same swizzled offset),
+//     so HBM / L2 traffic is that of the plain kernel: nothing is pre-split in global memory, no workspace.
+//   * epilogue: a warp can only read its own TMEM lane quadrant, so the warp holding a pixel row's hi lanes and the
+//     one holding its lo lanes each add their two column halves, exchange one partial through the staging tile and
+//     each finishes (transpose + coalesced 441-channel store) one b-row of every pair of b-rows they share.
+// Cost: 4x the tensor work of the tf32 kernel per output, for an output that meets the fp32 tolerance
+// (1e-5 relative + 1e-6 absolute against a float64 evaluation).
+//
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = epilogue (one
+// per TMEM lane quadrant), warps 6-9 = converters.
+#include <algorithm>
+#include "fn2_tc.cuh"
+
+namespace fn2 {
+namespace {
+
+using namespace tc;
+
+constexpr int XR = 2;                   // a-rows per tile (class space)
+constexpr int TILE_C = 32;              // a-cols per tile
+constexpr int A_HALF = 64 * 128;        // 64 a-pixels x 32 channels fp32 = 8 KB (raw; the lo copy follows it)
+constexpr int A_CHUNK = 2 * A_HALF;     // M = 128 operand rows of one 32-channel chunk
+constexpr int B_HALF = 128 * 128;       // 128 b-pixels x 32 channels = 16 KB (raw; the lo copy follows it)
+constexpr int B_STAGE = 2 * B_HALF;     // N = 256 operand rows of one 32-channel chunk
+constexpr int NSTAGE = 2;               // B ring depth
+constexpr int NBUF = 2;                 // TMEM accumulator buffers (2 x 256 columns = 512)
+constexpr int BUF_COLS = 256;
+constexpr int MAX_KC = 8;               // C <= 256
+constexpr int NEPI = 4;                 // epilogue warps: (a-row, hi/lo lanes) = one per TMEM lane quadrant
+constexpr int NCONV = 4;                // converter warps
+constexpr int NTHREADS = 64 + 32 * NEPI + 32 * NCONV;
+constexpr int STG_FLOATS = 32 * 33;     // transposed staging tile [b column][a column], pitch 33
+
+struct X3Params {
+  CUtensorMap a[4];   // per parity class, boxes of 2 rows x 32 cols x 32 channels
+  CUtensorMap b[4];   // per parity class, boxes of 4 rows x 32 cols x 32 channels
+  float* out;
+  int N, H, W, C, D, s2, ncls;
+  int Hc[2], Wc[2];   // class-space extent per parity
+  int Hcb[2];         // class-space rows of b (>= Hc + boff when b carries row halos)
+  int boff;           // class-space row of b that a-row 0 meets at displacement 0
+  int TY, TX;
+  int nkc;            // C / 32
+  float sumelems;
+  int opitch;         // floats between consecutive pixels of the output
+  float slope;        // fused LeakyReLU (1 = none)
+};
+
+struct __align__(8) X3Barriers {
+  uint64_t a_full;            // TMA: the raw a tile has landed
+  uint64_t a_conv;            // converters: its lo half is written
+  uint64_t full[NSTAGE];      // TMA: raw b chunk landed
+  uint64_t conv[NSTAGE];      // converters: lo b chunk written
+  uint64_t empty[NSTAGE];     // MMAs have read the stage
+  uint64_t tmem_full[NBUF];
+  uint64_t tmem_empty[NBUF];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// 32 lanes x 32 columns of BOTH column halves of an accumulator buffer, summed: (x raw b) + (x lo b)
+__device__ __forceinline__ void tmem_ld32_sum2(uint32_t taddr, float (&v)[32]) {
+  float w[16];   // the second half in two pieces: fewer live registers
+  tmem_ld32(taddr, v);
+  tmem_ld16(taddr + 128u, w);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] += w[j];
+  tmem_ld16(taddr + 144u, w);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[16 + j] += w[j];
+}
+
+// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 32 KB][staging: NEPI x 32x33 floats][barriers]
+template <int R, bool WIDE>
+__global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __grid_constant__ X3Params P) {
+  constexpr int GW = 2 * R + 1;
+  constexpr int NHX = WIDE ? 2 : 1;                 // 32-column b blocks per group of 4 b-rows
+  constexpr int XO0 = WIDE ? -16 : 0;               // column origin of the first one, relative to the a tile
+  constexpr int NTT = WIDE ? (GW * 16 + 31) / 32 : GW;  // store instructions per (a-row, b-row, block)
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)P.nkc * A_CHUNK;
+  float* sStage = reinterpret_cast<float*>(sB + (size_t)NSTAGE * B_STAGE);
+  X3Barriers* bars = reinterpret_cast<X3Barriers*>(sStage + NEPI * STG_FLOATS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- which tile ----
+  int t = blockIdx.x;
+  const int tx = t % P.TX; t /= P.TX;
+  const int ty = t % P.TY; t /= P.TY;
+  const int cls = t % P.ncls;
+  const int n = t / P.ncls;
+  const int cy = cls / P.s2, cx = cls % P.s2;
+  const int Hc = P.Hc[cy], Wc = P.Wc[cx];
+  const int y0 = ty * XR, x0 = tx * TILE_C;
+  if (y0 >= Hc || x0 >= Wc) return;  // whole CTA leaves together, before any barrier exists
+  const int Hcb = P.Hcb[cy];
+  const int s_first = max(0, y0 + P.boff - R);
+  const int s_last = min(Hcb - 1, y0 + P.boff + XR - 1 + R);
+  const int nblk = max(0, (s_last - s_first + 1 + 3) / 4) * NHX;   // blocks of 4 b-rows x 32 b-columns
+  const int nkc = P.nkc;
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bars->a_full), 1);
+    mbar_init(smem_u32(&bars->a_conv), NCONV);
+    for (int i = 0; i < NSTAGE; ++i) {
+      mbar_init(smem_u32(&bars->full[i]), 1);
+      mbar_init(smem_u32(&bars->conv[i]), NCONV);
+      mbar_init(smem_u32(&bars->empty[i]), 1);
+    }
+    for (int i = 0; i < NBUF; ++i) { mbar_init(smem_u32(&bars->tmem_full[i]), 1); mbar_init(smem_u32(&bars->tmem_empty[i]), NEPI); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (elect_one()) {
+      const uint32_t a_full = smem_u32(&bars->a_full);
+      mbar_expect_tx(a_full, (uint32_t)nkc * A_HALF);
+      for (int kc = 0; kc < nkc; ++kc)
+        tma_load_4d(smem_u32(sA + (size_t)kc * A_CHUNK), &P.a[cls], a_full, kc * KCH, x0, y0, n);
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int srow = s_first + (blk / NHX) * 4;
+        const int xcol = x0 + XO0 + (blk % NHX) * 32;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % NSTAGE;
+          mbar_wait(smem_u32(&bars->empty[stage]), ((it / NSTAGE) & 1) ^ 1);
+          const uint32_t full = smem_u32(&bars->full[stage]);
+          mbar_expect_tx(full, B_HALF);
+          tma_load_4d(smem_u32(sB + (size_t)stage * B_STAGE), &P.b[cls], full, kc * KCH, xcol, srow, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (elect_one()) {
+      constexpr uint32_t idesc = idesc_tf32(128, BUF_COLS);
+      if (nblk > 0) {
+        mbar_wait(smem_u32(&bars->a_full), 0);
+        mbar_wait(smem_u32(&bars->a_conv), 0);
+        tc_fence_after();
+      }
+      int it = 0;
+      for (int blk = 0; blk < nblk; ++blk) {
+        const int buf = blk % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((blk / NBUF) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)buf * BUF_COLS;
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          const int stage = it % NSTAGE;
+          const uint32_t par = (it / NSTAGE) & 1;
+          mbar_wait(smem_u32(&bars->full[stage]), par);
+          mbar_wait(smem_u32(&bars->conv[stage]), par);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + (size_t)kc * A_CHUNK);
+          const uint32_t b_addr = smem_u32(sB + (size_t)stage * B_STAGE);
+#pragma unroll
+          for (int k4 = 0; k4 < 4; ++k4)  // K = 8 tf32 = 32 bytes per instruction inside the 128-byte swizzle row
+            umma_tf32(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
+                      (uint32_t)((kc | k4) != 0));
+          umma_commit(smem_u32(&bars->empty[stage]));   // frees the B stage (raw and lo) when these MMAs have read it
+        }
+        umma_commit(smem_u32(&bars->tmem_full[buf]));   // accumulator block complete
+      }
+    }
+  } else if (warp < 2 + NEPI) {
+    // ================================ epilogue (warps 2..5) ================================
+    const int q = warp & 3;              // TMEM lane quadrant this warp may read
+    const int ar = q & 1;                // a-row of the tile
+    const int isLo = q >> 1;             // quadrants 2, 3 hold the products of a_lo
+    // The hi warp and the lo warp of an a-row share two staging tiles.  Of the b-rows (half, half + 2) of a block,
+    // tile 0 collects b-row `half` (finished by the hi warp), tile 1 b-row `half + 2` (finished by the lo warp).
+    float* mine = sStage + (ar * 2 + isLo) * STG_FLOATS;
+    float* theirs = sStage + (ar * 2 + (isLo ^ 1)) * STG_FLOATS;
+    const int y = y0 + ar;               // class-space row of this warp's 32 pixels
+    const bool row_ok = y < Hc;
+    const int Y = y * P.s2 + cy;         // full-resolution row
+    const int ncol = min(TILE_C, Wc - x0);
+    const float inv = 1.0f / P.sumelems;
+    float* orow0 = P.out + (((size_t)n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(x0 * P.s2 + cx)) * P.opitch;
+    const int pixstride = P.s2 * P.opitch;    // floats between neighbouring pixels of the class
+
+    // Per-lane plan for writing one displacement row (32 pixels x GW values, 84-byte runs) coalesced; see
+    // corr_tc_fwd_kernel (corr_tc.cu) for the enumeration.
+    // One packed word per store: pixel column cc [0,5), displacement o [5,10), b column xb [10,15), bit 15 = the
+    // b column lies inside the block (else the value is a lateral zero), bit 16 = the store is live.
+    uint32_t plan[NHX][NTT];
+#pragma unroll
+    for (int hx = 0; hx < NHX; ++hx) {
+      const int XO = XO0 + 32 * hx;
+#pragma unroll
+      for (int tt = 0; tt < NTT; ++tt) {
+        const int e = tt * 32 + lane;
+        int cc, o;
+        bool live = true;
+        if (!WIDE) {
+          cc = e / GW; o = e - cc * GW;
+        } else {
+          int acc = 0; cc = 0; o = 0; live = false;
+#pragma unroll 1
+          for (int c2 = 0; c2 < 32; ++c2) {
+            const int lo = max(0, R + XO - c2), hi = min(GW - 1, R + XO + 31 - c2);
+            const int cnt = max(0, hi - lo + 1);
+            if (!live && e < acc + cnt) { cc = c2; o = lo + (e - acc); live = true; }
+            acc += cnt;
+          }
+        }
+        const int xb = cc + o - R - XO;
+        const bool xok = (xb >= 0) && (xb < 32);
+        plan[hx][tt] = (uint32_t)cc | ((uint32_t)o << 5) | ((uint32_t)(xok ? xb : 0) << 10) | ((xok ? 1u : 0u) << 15) |
+                       (((live && cc < ncol) ? 1u : 0u) << 16);
+      }
+    }
+
+    // displacement rows that point outside the image: written as zeros here, never computed
+    if (row_ok) {
+      const int yb = y + P.boff;                          // b-row this a-row meets at p = 0
+      const int dlo = min(GW, max(0, R - yb)) * GW;       // p < -yb
+      const int dhi = max(0, min(GW, Hcb - yb + R)) * GW; // p > Hcb-1-yb
+      for (int cc = isLo; cc < ncol; cc += 2) {
+        float* po = orow0 + (size_t)cc * pixstride;
+        for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
+        for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
+      }
+    }
+
+    for (int blk0 = 0; blk0 < nblk; blk0 += NHX) {
+#pragma unroll
+      for (int hx = 0; hx < NHX; ++hx) {
+        const int blk = blk0 + hx;
+        const int buf = blk % NBUF;
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
+        tc_fence_after();
+        const int sbase = s_first + (blk0 / NHX) * 4;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BUF_COLS);
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+          const int brMine = half + 2 * isLo, brTheirs = half + 2 * (isLo ^ 1);
+          const int sM = sbase + brMine, sT = sbase + brTheirs;
+          const int pM = sM - (y + P.boff), pT = sT - (y + P.boff);
+          const bool okM = row_ok && pM >= -R && pM <= R && sM < Hcb;   // the same in both warps of the pair
+          const bool okT = row_ok && pT >= -R && pT <= R && sT < Hcb;
+          float vm[32];
+          if (okT) {   // the partner finishes this b-row: hand it this warp's partial sum
+            float v[32];
+            tmem_ld32_sum2(tbase + (uint32_t)(brTheirs * 32), v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) theirs[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+          }
+          if (okM) tmem_ld32_sum2(tbase + (uint32_t)(brMine * 32), vm);
+          named_bar_sync(1 + ar, 64);      // both partial sums are in the tiles
+          if (okM) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) mine[j * 33 + lane] += vm[j];   // same lane, same word the partner wrote
+            __syncwarp();
+            float* orow = orow0 + (pM + R) * GW;
+#pragma unroll
+            for (int tt = 0; tt < NTT; ++tt) {
+              const uint32_t pl = plan[hx][tt];
+              const int cc = pl & 31u, o = (pl >> 5) & 31u, xb = (pl >> 10) & 31u;
+              float x = mine[xb * 33 + cc];
+              x = ((pl >> 15) & 1u) ? x * inv : 0.f;
+              x = x > 0.f ? x : x * P.slope;
+              if ((pl >> 16) & 1u) orow[cc * pixstride + o] = x;
+            }
+          }
+          named_bar_sync(1 + ar, 64);      // the tiles may be overwritten
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
+      }
+    }
+  } else {
+    // ================================ converters (warps 6..9): lo = x - tf32(x) ================================
+    const int ct = threadIdx.x - (64 + 32 * NEPI);
+    constexpr int NCT = 32 * NCONV;
+    mbar_wait(smem_u32(&bars->a_full), 0);
+    for (int kc = 0; kc < nkc; ++kc) {
+      uint8_t* base = sA + (size_t)kc * A_CHUNK;
+#pragma unroll
+      for (int i = 0; i < A_HALF / 16 / NCT; ++i) {
+        const int off = (ct + i * NCT) * 16;
+        const float4 v = *reinterpret_cast<const float4*>(base + off);
+        *reinterpret_cast<float4*>(base + A_HALF + off) = x3_lo4(v);
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+    __syncwarp();
+    if (lane == 0) mbar_arrive(smem_u32(&bars->a_conv));
+    const int nit = nblk * nkc;
+    for (int it = 0; it < nit; ++it) {
+      const int stage = it % NSTAGE;
+      mbar_wait(smem_u32(&bars->full[stage]), (it / NSTAGE) & 1);
+      uint8_t* base = sB + (size_t)stage * B_STAGE;
+      float4 v[B_HALF / 16 / NCT];
+#pragma unroll
+      for (int i = 0; i < B_HALF / 16 / NCT; ++i) v[i] = *reinterpret_cast<const float4*>(base + (ct + i * NCT) * 16);
+#pragma unroll
+      for (int i = 0; i < B_HALF / 16 / NCT; ++i)
+        *reinterpret_cast<float4*>(base + B_HALF + (ct + i * NCT) * 16) = x3_lo4(v[i]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars->conv[stage]));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+size_t x3_smem_bytes(int nkc) {
+  return 1024 + (size_t)nkc * A_CHUNK + (size_t)NSTAGE * B_STAGE + (size_t)NEPI * STG_FLOATS * sizeof(float) +
+         sizeof(X3Barriers);
+}
+
+}  // namespace
+
+int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st) {
+  X3Params P;
+  P.out = out;
+  P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.D = g.D; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
+  P.boff = g.bTop / g.s2;
+  for (int c = 0; c < 2; ++c) {
+    P.Hc[c] = c < g.s2 ? (g.H - c + g.s2 - 1) / g.s2 : 0;
+    P.Wc[c] = c < g.s2 ? (g.W - c + g.s2 - 1) / g.s2 : 0;
+    P.Hcb[c] = c < g.s2 ? (g.bH - c + g.s2 - 1) / g.s2 : 0;
+  }
+  P.TY = (P.Hc[0] + XR - 1) / XR;
+  P.TX = (P.Wc[0] + TILE_C - 1) / TILE_C;
+  P.nkc = g.C / KCH;
+  P.sumelems = (float)g.C;
+  P.opitch = g.oPitch;
+  P.slope = g.slope;
+  for (int cls = 0; cls < P.ncls; ++cls) {
+    const int cy = cls / g.s2, cx = cls % g.s2;
+    if (P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // empty class (H or W == 1 with s2 == 2): map class 0 instead, never used
+      P.a[cls] = P.a[0]; P.b[cls] = P.b[0];
+      continue;
+    }
+    if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, XR) ||
+        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 4))
+      return FN2_E_CUDA;
+  }
+  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }
+  static PerDeviceOnce once;
+  const cudaError_t attr_err = per_device_once(once, [] {
+    cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_x3_kernel<10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)x3_smem_bytes(MAX_KC));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(corr_tc_fwd_x3_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               (int)x3_smem_bytes(MAX_KC));
+    return e;
+  });
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
+  if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
+  const size_t smem = x3_smem_bytes(P.nkc);
+  if (P.TX > 1)
+    corr_tc_fwd_x3_kernel<10, true><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  else
+    corr_tc_fwd_x3_kernel<10, false><<<(unsigned)grid, NTHREADS, smem, st>>>(P);
+  return after_launch();
+}
+
+}  // namespace fn2

@@ -416,12 +416,11 @@ bool band_plan(const DsParams& p, BandPlan* bp) {
 template <int CT, int PX, int U>
 int launch_band(const DsParams& p, const BandPlan& bp, const float* in, float* out, cudaStream_t st) {
   auto kern = downsample_band_kernel<CT, PX, U>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  static PerDeviceOnce once;   // one per template instantiation; function attributes are per device
+  const cudaError_t attr_err = per_device_once(once, [&] {
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   });
-  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)bp.rs, (unsigned)((p.oH + bp.G - 1) / bp.G), (unsigned)p.N);
   cfg.blockDim = dim3((unsigned)band_threads(p, PX));

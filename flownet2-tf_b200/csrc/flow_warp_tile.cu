@@ -465,21 +465,21 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_bwd(const __grid_constant__ C
 template <int C>
 int launch_tile(int mode, const float* image, const float* flow, const float* gout, float* out, float* out2, int N,
                 int H, int W, cudaStream_t st) {
-  static std::once_flag once;
-  static cudaError_t err = cudaSuccess;
-  std::call_once(once, [] {
+  static PerDeviceOnce once;   // per template instantiation; function attributes are per device
+  const cudaError_t err = per_device_once(once, [] {
     const int bytes = (int)Win<C>::BYTES;
-    err = cudaFuncSetAttribute(warp_tile_gather<C, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (err == cudaSuccess)
-      err = cudaFuncSetAttribute(warp_tile_gather<C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (err == cudaSuccess)
-      err = cudaFuncSetAttribute(warp_tile_gather<C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (err == cudaSuccess)
-      err = cudaFuncSetAttribute(warp_tile_scatter<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-    if (err == cudaSuccess)
-      err = cudaFuncSetAttribute(warp_tile_bwd<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    cudaError_t e = cudaFuncSetAttribute(warp_tile_gather<C, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(warp_tile_gather<C, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(warp_tile_gather<C, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(warp_tile_scatter<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(warp_tile_bwd<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    return e;
   });
-  if (err != cudaSuccess) { note_cuda_error(err); return FN2_E_CUDA; }
+  if (err != cudaSuccess) { note_cuda_error(err); (void)cudaGetLastError(); return FN2_E_CUDA; }
   const int tilesX = (W + TW - 1) / TW, tilesY = (H + TH - 1) / TH;
   const long long blocks = (long long)N * tilesX * tilesY;
   if (blocks > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
@@ -530,7 +530,7 @@ int flow_warp_tile_forward_error(const float* image, const float* flow, const fl
 // gimage must already be zero (flow_warp_backward memsets it on the same stream)
 int flow_warp_tile_backward(const float* image, const float* flow, const float* gout, float* gimage, float* gflow,
                             int N, int H, int W, int C, cudaStream_t st) {
-  if (!getenv("FN2_WARP_BWD_SPLIT")) return dispatch_tile(4, image, flow, gout, gflow, N, H, W, C, st, gimage);
+  if (!env_switches().warp_bwd_split) return dispatch_tile(4, image, flow, gout, gflow, N, H, W, C, st, gimage);
   const int rc = dispatch_tile(1, image, flow, gout, gflow, N, H, W, C, st);
   if (rc != FN2_OK) return rc;
   return dispatch_tile(2, nullptr, flow, gout, gimage, N, H, W, C, st);

@@ -2,6 +2,7 @@
 // reference OpKernels, then dispatch to the sm_100a kernels.  No allocation, no host synchronisation.
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include "fn2_common.cuh"
 
 namespace fn2 {
@@ -19,6 +20,35 @@ int after_launch() {
     return FN2_E_CUDA;
   }
   return FN2_OK;
+}
+
+int device_sm_count() {
+  static std::atomic<int> cache[FN2_MAX_DEVICES];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  const bool tracked = dev >= 0 && dev < FN2_MAX_DEVICES;
+  if (tracked) {
+    const int c = cache[dev].load(std::memory_order_relaxed);
+    if (c > 0) return c;
+  }
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms < 1) return 148;
+  if (tracked) cache[dev].store(sms, std::memory_order_relaxed);
+  return sms;
+}
+
+const EnvSwitches& env_switches() {
+  static const EnvSwitches sw = [] {
+    EnvSwitches s;
+    s.no_pair = getenv("FN2_NO_PAIR") != nullptr;
+    s.no_split = getenv("FN2_NO_SPLIT") != nullptr;
+    s.no_persist = getenv("FN2_NO_PERSIST") != nullptr;
+    s.warp_bwd_split = getenv("FN2_WARP_BWD_SPLIT") != nullptr;
+    const char* e = getenv("FN2_DS_MAX_RANKS");
+    s.ds_max_ranks = e ? atoi(e) : 0;
+    return s;
+  }();
+  return sw;
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -102,6 +132,16 @@ int fn2_correlation_output_shape(int H, int W, int k, int md, int s1, int s2, in
   return FN2_OK;
 }
 
+int fn2_correlation_precision_supported(int N, int H, int W, int C, int k, int md, int s1, int s2, int pad,
+                                        int precision) {
+  CorrGeom g;
+  const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (precision == FN2_PREC_FP32) return 1;
+  if (precision != FN2_PREC_TF32 && precision != FN2_PREC_TF32X3) return 0;
+  return corr_tc_supported(g, precision) ? 1 : 0;
+}
+
 size_t fn2_correlation_workspace_bytes(int N, int H, int W, int C, int k, int md, int s1, int s2, int pad,
                                        int precision, int direction) {
   CorrGeom g;
@@ -131,7 +171,9 @@ int fn2_correlation_forward_fused(const float* a, const float* b, float* out, in
   const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
   if (rc != FN2_OK) return rc;
   if (out_pixel_pitch < g.D) return FN2_E_BAD_SHAPE;
-  if (!(leaky_slope == leaky_slope)) return FN2_E_BAD_PARAM;
+  // The backward of the fused activation recovers its mask from the sign of the stored output, which needs slope > 0
+  // (the reference's LeakyReLU is 0.1, utils.py:401-405); NaN is rejected by the same test.
+  if (!(leaky_slope > 0.f)) return FN2_E_BAD_PARAM;
   g.oPitch = out_pixel_pitch;
   g.slope = leaky_slope;
   return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
@@ -163,10 +205,8 @@ static int correlation_forward(const CorrGeom& g, const float* a, const float* b
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (precision) {
     case FN2_PREC_FP32:
-      if (corr_simt_supported(g)) return corr_simt_forward(g, a, b, out, st);
       return corr_generic_forward(g, a, b, out, st);   // handles row halos too
     case FN2_PREC_TF32:
-    case FN2_PREC_BF16:
     case FN2_PREC_TF32X3:
       if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
       if (ws_bytes < corr_tc_workspace_bytes(g, precision, 0) || (ws_bytes && !ws)) return FN2_E_WORKSPACE;
@@ -192,10 +232,8 @@ static int correlation_backward(const CorrGeom& g, const float* gout, const floa
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (precision) {
     case FN2_PREC_FP32:
-      if (corr_simt_supported(g)) return corr_simt_backward(g, gout, a, b, ga, gb, st);
       return corr_generic_backward(g, gout, a, b, ga, gb, st);
     case FN2_PREC_TF32:
-    case FN2_PREC_BF16:
     case FN2_PREC_TF32X3:
       if (!corr_tc_supported(g, precision)) return FN2_E_UNSUPPORTED_PRECISION;
       if (ws_bytes < corr_tc_workspace_bytes(g, precision, 1) || (ws_bytes && !ws)) return FN2_E_WORKSPACE;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <atomic>
 #include "../../include/fn2ops.h"
 
 #if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
@@ -31,24 +32,47 @@ struct CorrGeom {
 int after_launch();
 void note_cuda_error(cudaError_t e);
 
+// One-time set-up that CUDA keeps PER DEVICE (cudaFuncSetAttribute: opt-in shared memory, non-portable cluster sizes).
+// One flag per device ordinal; a failed attempt is not latched, and a process that moves from cuda:0 to cuda:1 runs
+// the set-up again there.  Idempotent, so two threads racing on the first call of a device are harmless.
+constexpr int FN2_MAX_DEVICES = 64;
+struct PerDeviceOnce {
+  std::atomic<int> done[FN2_MAX_DEVICES];
+};
+template <class F>
+inline cudaError_t per_device_once(PerDeviceOnce& flags, F&& setup) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  const bool tracked = dev >= 0 && dev < FN2_MAX_DEVICES;
+  if (tracked && flags.done[dev].load(std::memory_order_acquire)) return cudaSuccess;
+  e = setup();
+  if (e == cudaSuccess && tracked) flags.done[dev].store(1, std::memory_order_release);
+  return e;
+}
+// SM count of the current device (cached per device ordinal; 148 on B200).
+int device_sm_count();
+// Developer A/B switches: environment variables read ONCE, when the library is first asked (never per launch).
+struct EnvSwitches {
+  bool no_pair, no_split, no_persist, warp_bwd_split;
+  int ds_max_ranks;   // 0 = unset
+};
+const EnvSwitches& env_switches();
+
 // ---- kernels (one translation unit each) ------------------------------------------------------------------
 int corr_generic_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st);
 int corr_generic_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
                           float* gb, cudaStream_t st);
 
-// fp32 CUDA-core kernels for kernel_size == 1, stride_1 == 1 (the FlowNetC call, flownet_c.py:40)
-bool corr_simt_supported(const CorrGeom& g);
-int corr_simt_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st);
-int corr_simt_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
-                       cudaStream_t st);
-
-// tcgen05 kernels (tf32 / 3xTF32 / bf16)
+// tcgen05 kernels (tf32 / split-tf32)
 bool corr_tc_supported(const CorrGeom& g, int precision);
 size_t corr_tc_workspace_bytes(const CorrGeom& g, int precision, int direction);
 int corr_tc_forward(const CorrGeom& g, const float* a, const float* b, float* out, int precision, void* ws,
                     size_t ws_bytes, cudaStream_t st);
 int corr_tc_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,
                      int precision, void* ws, size_t ws_bytes, cudaStream_t st);
+// corr_tc_x3.cu: fp32-grade forward (split-tf32)
+int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float* out, cudaStream_t st);
 // corr_tc_bwd.cu
 bool corr_tc_bwd_supported(const CorrGeom& g, int precision);
 int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga, float* gb,

@@ -117,6 +117,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 32 lanes x 16 consecutive columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 // One lane of the (fully active) warp, chosen by hardware.  Branching on this predicate -- instead of on lane == 0 --
 // tells ptxas that exactly one thread runs the branch, so single-thread instructions (tcgen05.mma, tcgen05.commit,
 // TMA) are emitted straight instead of inside a per-active-lane ELECT loop.
@@ -282,6 +297,21 @@ __device__ __forceinline__ uint64_t desc_sw128b32_mnmajor(uint32_t saddr, uint32
 __host__ __device__ constexpr uint32_t idesc_tf32_major(int M, int N, int a_mn, int b_mn) {
   return idesc_tf32(M, N) | ((uint32_t)(a_mn & 1) << 15) | ((uint32_t)(b_mn & 1) << 16);
 }
+
+// ---------------------------------------------------------------------------------------------- 3xTF32 split
+// kind::tf32 reads an fp32 word as tf32 by IGNORING its low 13 mantissa bits, so the raw fp32 bits already are the
+// "hi" operand: hi = x with those bits cleared.  lo = x - hi is exact in fp32 (at most 13 significant bits); it is
+// rounded to nearest on 11 significant bits here so that the tensor core's truncation of lo loses nothing more.
+//   x * y  ~=  hi_x*hi_y + lo_x*hi_y + hi_x*lo_y (+ lo_x*lo_y)      relative error ~2^-21 per product
+// Inf / NaN: hi carries them; lo must not turn inf into inf - inf = NaN.
+__device__ __forceinline__ float x3_lo(float x) {
+  const uint32_t u = __float_as_uint(x);
+  float l = x - __uint_as_float(u & 0xffffe000u);
+  l = __uint_as_float((__float_as_uint(l) + 0x1000u) & 0xffffe000u);
+  if ((u & 0x7f800000u) == 0x7f800000u) l = (u & 0x007fffffu) ? x : 0.f;
+  return l;
+}
+__device__ __forceinline__ float4 x3_lo4(float4 v) { return make_float4(x3_lo(v.x), x3_lo(v.y), x3_lo(v.z), x3_lo(v.w)); }
 
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

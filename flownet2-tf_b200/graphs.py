@@ -28,7 +28,7 @@ import torch.nn.functional as F
 LOSS_WEIGHTS = (0.32, 0.08, 0.02, 0.01, 0.005)   # predict_flow6 .. predict_flow2 (flownet_c.py:163)
 
 
-def default_ops(precision="tf32"):
+def default_ops(precision=None):
     """This package's CUDA ops behind the reference's three signatures (+ the fused multi-scale downsample)."""
     from .correlation import correlation as _correlation, correlation_leaky_concat as _fused
     from .flow_warp import flow_warp as _flow_warp, flow_warp_error as _flow_warp_error
@@ -164,7 +164,7 @@ def _to_cl(x_nhwc):
 class FlowNetC(nn.Module):
     """flownet_c.py:15-125."""
 
-    def __init__(self, ops=None, precision="tf32"):
+    def __init__(self, ops=None, precision=None):
         super().__init__()
         self.ops = ops if ops is not None else default_ops(precision)
         self.conv1 = Conv(3, 64, 7, 2)
@@ -296,7 +296,7 @@ class FlowNetCS(nn.Module):
     """flownet_cs.py:15-38: FlowNetC with frozen weights (trainable=False, :18), then FlowNetS on
     [a, b, warp(b, flow_C), flow_C * 0.05, brightness error]."""
 
-    def __init__(self, ops=None, precision="tf32"):
+    def __init__(self, ops=None, precision=None):
         super().__init__()
         self.ops = ops if ops is not None else default_ops(precision)
         self.net_c = FlowNetC(self.ops)
@@ -313,7 +313,7 @@ class FlowNetCS(nn.Module):
 class FlowNetCSS(nn.Module):
     """flownet_css.py:15-38: FlowNetCS frozen, then a second FlowNetS."""
 
-    def __init__(self, ops=None, precision="tf32"):
+    def __init__(self, ops=None, precision=None):
         super().__init__()
         self.ops = ops if ops is not None else default_ops(precision)
         self.net_cs = FlowNetCS(self.ops)
@@ -332,7 +332,7 @@ class FlowNet2(nn.Module):
     and both image differences, 11-channel input to the fusion net, whose transposed convolutions DO have biases
     (no biases_initializer=None scope there, :50-98); predict_flow0 at full resolution."""
 
-    def __init__(self, ops=None, precision="tf32"):
+    def __init__(self, ops=None, precision=None):
         super().__init__()
         self.ops = ops if ops is not None else default_ops(precision)
         self.net_css = FlowNetCSS(self.ops)
@@ -387,6 +387,15 @@ def average_endpoint_error(labels, predictions):
     return torch.sqrt(torch.sum(d * d, dim=3)).sum() / predictions.shape[0]
 
 
+def weighted_loss(losses, weights):
+    """tf.losses.compute_weighted_loss(losses, weights) with its default reduction SUM_BY_NONZERO_WEIGHTS
+    (flownet_c.py:163): sum_i w_i * l_i divided by the number of non-zero weights -- 5 for the FlowNet losses, so
+    the data term is a fifth of the plain weighted sum relative to the L2 regulariser."""
+    nonzero = sum(1 for w in weights if w != 0)
+    total = sum(w * l for w, l in zip(weights, losses))
+    return total / nonzero if nonzero else total * 0.0
+
+
 def multiscale_loss(flow, predictions, ops, gt_scale=0.05, weights=LOSS_WEIGHTS):
     """The training loss of FlowNetC / S (gt_scale 0.05: flownet_c.py:127-166, flownet_s.py:122-161) and SD
     (gt_scale 20.0: flownet_sd.py:121-160): the ground-truth flow, scaled, is downsampled to the size of each of
@@ -400,7 +409,7 @@ def multiscale_loss(flow, predictions, ops, gt_scale=0.05, weights=LOSS_WEIGHTS)
     else:
         downs = [ops.downsample(flow, list(s)) for s in sizes]
     losses = [average_endpoint_error(d, p) for d, p in zip(downs, preds)]
-    return sum(w * l for w, l in zip(weights, losses)), losses
+    return weighted_loss(losses, weights), losses
 
 
 def l2_regularization(module, scale):

@@ -37,10 +37,10 @@ def _geom(a, k, md, s1, s2, pad):
 
 def correlation_halo_forward(a, b_ext, k, md, s1, s2, pad, halo_top, halo_bottom, precision=None):
     """out rows of one strip: ``a`` [N,H,W,C], ``b_ext`` [N,H+halo_top+halo_bottom,W,C] (fn2ops.h, *_halo)."""
-    prec = _prec(precision)
     _lib.require_cuda_f32(a, "input_a")
     _lib.require_cuda_f32(b_ext, "input_b")
     N, H, W, C = a.shape
+    prec = _prec(precision, _geom(a, k, md, s1, s2, pad))
     if tuple(b_ext.shape) != (N, H + halo_top + halo_bottom, W, C):
         raise ValueError("input_b must have shape %s, got %s" % ((N, H + halo_top + halo_bottom, W, C),
                                                                  tuple(b_ext.shape)))
@@ -58,9 +58,9 @@ def correlation_halo_forward(a, b_ext, k, md, s1, s2, pad, halo_top, halo_bottom
 
 def correlation_halo_backward(gradients, a, b_ext, k, md, s1, s2, pad, halo_top, halo_bottom, precision=None):
     """(backprops_a [N,H,W,C], backprops_b_ext [N,H+halo_top+halo_bottom,W,C]) of one strip."""
-    prec = _prec(precision)
     for t, name in ((gradients, "gradients"), (a, "input_a"), (b_ext, "input_b")):
         _lib.require_cuda_f32(t, name)
+    prec = _prec(precision, _geom(a, k, md, s1, s2, pad))
     ga = torch.empty_like(a)
     gb = torch.empty_like(b_ext)
     geom = _geom(a, k, md, s1, s2, pad)

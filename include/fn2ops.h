@@ -50,12 +50,17 @@ typedef enum fn2_status {
                                   halo_top a multiple of stride_2                                       */
 } fn2_status;
 
-/* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode. */
+/* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode.
+ * The reference op is float32 only (correlation_op.cc:54-61); FP32 and TF32X3 meet its tolerance (1e-5 relative +
+ * 1e-6 absolute against a float64 evaluation), TF32 trades accuracy (2.5e-3 of the tensor's maximum) for speed.
+ * The tensor-core modes cover the FlowNetC call shape (kernel_size 1, stride_1 1, pad == max_displacement,
+ * max_displacement / stride_2 == 10, stride_2 in {1, 2}, C a multiple of 32 and <= 256: flownet_c.py:40); ask
+ * fn2_correlation_precision_supported().  Value 2 is reserved (a bf16 mode is not built). */
 typedef enum fn2_precision {
-  FN2_PREC_FP32 = 0,   /* fp32 FMA on the CUDA cores; matches the reference within 1e-5 rel / 1e-6 abs      */
+  FN2_PREC_FP32 = 0,   /* fp32 FMA on the CUDA cores, any geometry                                          */
   FN2_PREC_TF32 = 1,   /* tcgen05 kind::tf32, fp32 accumulate in TMEM                                      */
-  FN2_PREC_BF16 = 2,   /* tcgen05 kind::f16 (bf16 operands), fp32 accumulate in TMEM                       */
-  FN2_PREC_TF32X3 = 3  /* tcgen05 3xTF32 split (hi*hi + hi*lo + lo*hi): fp32-grade result on tensor cores   */
+  FN2_PREC_TF32X3 = 3  /* tcgen05 split-tf32: operands split hi + lo, the partial products (hi*hi, hi*lo,
+                          lo*hi; the forward also lo*lo) accumulated in fp32: fp32-grade on tensor cores   */
 } fn2_precision;
 
 FN2_API int fn2_abi_version(void);
@@ -76,6 +81,11 @@ FN2_API int fn2_last_cuda_error(void);
 /* Shape function (correlation_op.cc:9-51, correlation_kernel.cc:35-57): out = [N, *out_h, *out_w, *out_c]. */
 FN2_API int fn2_correlation_output_shape(int H, int W, int kernel_size, int max_displacement, int stride_1, int stride_2,
                                  int pad, int* out_h, int* out_w, int* out_c);
+
+/* 1 if `precision` can run this call, 0 if not (fn2_correlation_* would return FN2_E_UNSUPPORTED_PRECISION), or a
+ * negative fn2_status for arguments the op itself rejects.  FN2_PREC_FP32 is supported for every valid call. */
+FN2_API int fn2_correlation_precision_supported(int N, int H, int W, int C, int kernel_size, int max_displacement,
+                                        int stride_1, int stride_2, int pad, int precision);
 
 /* Scratch bytes needed by the chosen precision (0 for FN2_PREC_FP32).  direction: 0 = forward, 1 = backward. */
 FN2_API size_t fn2_correlation_workspace_bytes(int N, int H, int W, int C, int kernel_size, int max_displacement,

@@ -59,6 +59,16 @@ def test_shape_function_and_error_codes():
     assert L.fn2_downsample_forward(None, None, 1, 8, 8, 2, 1, 4, None) == -9          # division by zero case
     assert L.fn2_downsample_forward(None, None, 1, 8, 8, 2, 4, 4, None) == -6
     assert L.fn2_correlation_workspace_bytes(1, 48, 64, 256, 1, 20, 1, 2, 20, 0, 0) == 0
+    # which arithmetic covers which call (no CUDA call involved)
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 1, 20, 1, 2, 20, 0) == 1
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 1, 20, 1, 2, 20, 1) == 1
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 1, 20, 1, 2, 20, 3) == 1
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 1, 20, 1, 2, 20, 2) == 0   # reserved value
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 3, 20, 1, 2, 20, 3) == 0   # kernel_size 3
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 100, 1, 20, 1, 2, 20, 1) == 0   # C % 32 != 0
+    assert L.fn2_correlation_precision_supported(1, 48, 64, 256, 2, 20, 1, 2, 20, 3) == -1  # the op's own error
+    assert L.fn2_correlation_forward_fused(16, 16, 16, 1, 48, 64, 256, 1, 20, 1, 2, 20, 473, -0.1, 1, None, 0,
+                                           None) == -5                                    # slope must be > 0
 
 
 def test_python_ops_reject_what_the_reference_rejects():

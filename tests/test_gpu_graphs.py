@@ -31,7 +31,7 @@ def _exact_convs():
     torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
-@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32x3", None, "tf32"])
 def test_flownet_c_forward_and_training_step_match_the_oracle_graph(precision):
     torch.manual_seed(0)
     cpu = G.FlowNetC(ops=oracle_ops())
@@ -58,9 +58,9 @@ def test_flownet_c_forward_and_training_step_match_the_oracle_graph(precision):
         assert rel <= (2e-2 if precision == "tf32" else 1e-3), (name, rel)
 
 
-@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("tf32", 1e-1)])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("tf32x3", 1e-3), (None, 1e-3), ("tf32", 1e-1)])
 def test_flownet2_stacked_inference_matches_the_oracle_graph(precision, tol):
-    """fp32 ops: the north_star's 1e-3 EPE.  tf32 correlation: random-init weights make the four stacked nets an
+    """fp32 and split-tf32 ops (and the default, None = "auto" = split-tf32 here): the north_star's 1e-3 EPE.  tf32 correlation: random-init weights make the four stacked nets an
     amplifier (flow magnitudes of several pixels out of 0.05-pixel features, two warps in between), so the 2e-4
     error of the tf32 cost volume grows to a few 1e-2 pixels at the end of the stack (measured 3.4e-2); 1e-1 stated."""
     torch.manual_seed(3)

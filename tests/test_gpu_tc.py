@@ -3,7 +3,9 @@
 Stated tolerances (BASELINE.json north_star: "the tf32/bf16 paths within a stated tolerance"):
   tf32   : |err| <= 2.5e-3 * max|ref|   (10-bit mantissa operands, fp32 accumulate over C = 256 products; measured
            worst case on these inputs is ~9e-4 * max|ref|, profiles/r01_b_check_tc_bwd.log)
-  tf32x3 : the fp32 tolerance of the op, 1e-5 relative / 1e-6 absolute (3xTF32 split, fp32-grade)
+  tf32x3 : the fp32 tolerance of the op, 1e-5 relative / 1e-6 absolute (split-tf32, fp32-grade): checked with
+           conftest.assert_close exactly like the fp32 CUDA-core kernels
+The same figure is stated in BASELINE.md section 4 and DESIGN.md section 2.
 """
 import numpy as np
 import pytest
@@ -45,6 +47,67 @@ def test_tf32_forward_backward_matches_oracle(shape):
     wga, wgb = o.c_correlation_grad(g.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
     assert _rel_to_max(ad.grad.cpu().numpy(), wga) <= TF32_TOL
     assert _rel_to_max(bd.grad.cpu().numpy(), wgb) <= TF32_TOL
+
+
+@pytest.mark.parametrize("shape", TC_SHAPES + [(2, 20, 140, 64), (1, 8, 70, 160)])   # + wide classes (TX > 1)
+def test_tf32x3_forward_backward_meets_the_fp32_tolerance(shape):
+    """The split-tf32 tensor-core path is held to the tolerance of the reference's own precision."""
+    N, H, W, C = shape
+    a, b = corr_inputs(N, H, W, C)
+    ad, bd = a.cuda().requires_grad_(), b.cuda().requires_grad_()
+    out = fn2.correlation(ad, bd, *ARGS, precision="tf32x3")
+    g = grad_like(out.shape)
+    out.backward(g.cuda())
+    want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
+    assert_close(out.detach().cpu().numpy(), want, rel=1e-5, abs_=1e-6, what="tf32x3 forward")
+    wga, wgb = o.c_correlation_grad(g.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
+    assert_close(ad.grad.cpu().numpy(), wga, rel=1e-5, abs_=1e-6, what="tf32x3 backprops_a")
+    assert_close(bd.grad.cpu().numpy(), wgb, rel=1e-5, abs_=1e-6, what="tf32x3 backprops_b")
+
+
+def test_tf32x3_large_dynamic_range_and_specials():
+    """Magnitudes from 1e-12 to 1e+12 (hi/lo split must not lose small operands or overflow), and an inf / NaN input
+    must come out as inf / NaN in exactly the outputs it touches, not as NaN everywhere (lo of inf is 0, not inf-inf)."""
+    N, H, W, C = 1, 12, 40, 64
+    g = torch.Generator().manual_seed(11)
+    scale = 10.0 ** torch.randint(-6, 7, (N, H, W, 1), generator=g).float()
+    a = torch.randn(N, H, W, C, generator=g) * scale
+    b = torch.randn(N, H, W, C, generator=g) * scale.flip(2)
+    out = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32x3").cpu().numpy()
+    want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
+    # per output the error scales with sum |a_c b_c| / C, which here can dwarf the (cancelling) sum itself
+    mag = o.c_correlation(a.abs().numpy(), b.abs().numpy(), *ARGS, f64=True)
+    assert (np.abs(out - want) <= 4e-6 * mag + 1e-30).all()
+    a2, b2 = corr_inputs(N, H, W, C)
+    a2[0, 4, 6, 3] = float("inf")
+    b2[0, 6, 20, 5] = float("nan")
+    out = fn2.correlation(a2.cuda(), b2.cuda(), *ARGS, precision="tf32x3").cpu().numpy()
+    want = o.c_correlation(a2.numpy(), b2.numpy(), *ARGS, f64=True)
+    assert (np.isnan(out) == np.isnan(want)).all() and (np.isinf(out) == np.isinf(want)).all()
+    ok = np.isfinite(want)
+    assert_close(out[ok], want[ok], rel=1e-5, abs_=1e-6, what="tf32x3 finite outputs next to inf/NaN inputs")
+
+
+@pytest.mark.parametrize("precision,check", [("tf32", "max"), ("tf32x3", "fp32")])
+def test_value_check_on_a_full_batch(precision, check):
+    """cfg3 batch (N = 32, the benchmarked launch): two pairs picked out of the batch are checked VALUE by value
+    against the f64 oracle, forward and both gradients (the other tests at this size check properties only)."""
+    N, H, W, C = 32, 48, 64, 256
+    a, b = corr_inputs(N, H, W, C)
+    g = grad_like((N, H, W, 441))
+    ad, bd, gd = a.cuda(), b.cuda(), g.cuda()
+    out = fn2.correlation(ad, bd, *ARGS, precision=precision)
+    ga, gb = fn2.correlation_grad(gd, ad, bd, *ARGS, precision=precision)
+    for n in (5, 29):
+        sl = slice(n, n + 1)
+        want = o.c_correlation(a[sl].numpy(), b[sl].numpy(), *ARGS, f64=True)
+        wga, wgb = o.c_correlation_grad(g[sl].numpy(), a[sl].numpy(), b[sl].numpy(), *ARGS, f64=True)
+        for got, ref_, what in ((out[sl], want, "forward"), (ga[sl], wga, "backprops_a"), (gb[sl], wgb, "backprops_b")):
+            got = got.cpu().numpy()
+            if check == "max":
+                assert _rel_to_max(got, ref_) <= TF32_TOL, (what, n)
+            else:
+                assert_close(got, ref_, rel=1e-5, abs_=1e-6, what="%s %s pair %d" % (precision, what, n))
 
 
 def test_tf32_exact_on_tf32_representable_inputs():
@@ -92,10 +155,47 @@ def test_tf32_full_size_properties():
     assert abs(lhs - prod.sum()) <= 5e-4 * prod.abs().sum()
 
 
-def test_unsupported_precision_is_an_error_not_a_fallback():
-    a = torch.zeros(1, 8, 8, 4, device="cuda")   # C % 32 != 0: no tensor-core tiling
-    with pytest.raises(ValueError, match="precision not supported"):
-        fn2.correlation(a, a, 1, 2, 1, 2, 2, precision="tf32")
+def test_unsupported_geometry_falls_back_to_fp32_with_a_warning_never_to_less_accuracy():
+    """The C ABI answers FN2_E_UNSUPPORTED_PRECISION (no silent switch inside the library); the Python op then runs the
+    fp32 CUDA-core kernels -- MORE accurate than what was asked for -- and says so.  There is still no CPU path."""
+    from flownet2_tf_b200 import _lib
+    a, b = corr_inputs(1, 8, 8, 4)     # C % 32 != 0: no tensor-core tiling
+    ad, bd = a.cuda(), b.cuda()
+    out = torch.empty(1, 8, 8, 9, device="cuda")
+    for prec in (1, 3):
+        assert _lib.lib().fn2_correlation_precision_supported(1, 8, 8, 4, 1, 2, 1, 2, 2, prec) == 0
+        rc = _lib.lib().fn2_correlation_forward(ad.data_ptr(), bd.data_ptr(), out.data_ptr(), 1, 8, 8, 4, 1, 2, 1, 2, 2,
+                                                prec, None, 0, None)
+        assert rc == -7
+    assert _lib.lib().fn2_correlation_precision_supported(1, 48, 64, 256, 1, 20, 1, 2, 20, 3) == 1
+    with pytest.warns(RuntimeWarning, match="fp32 CUDA-core"):
+        got = fn2.correlation(ad, bd, 1, 2, 1, 2, 2, precision="tf32")
+    assert torch.equal(got, fn2.correlation(ad, bd, 1, 2, 1, 2, 2, precision="fp32"))
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("error")                      # "auto" picks fp32 here silently
+        assert torch.equal(fn2.correlation(ad, bd, 1, 2, 1, 2, 2), got)
+
+
+def test_two_devices_in_one_process():
+    """Function attributes (opt-in shared memory, cluster sizes) are per device: a process that first runs on cuda:0
+    and then on cuda:1 must set them again there.  Skipped on a one-GPU box."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    a, b = corr_inputs(2, 24, 32, 64)
+    res = []
+    for dev in ("cuda:0", "cuda:1"):
+        ad, bd = a.to(dev), b.to(dev)
+        out = fn2.correlation(ad, bd, *ARGS, precision="tf32x3")
+        ga, gb = fn2.correlation_grad(torch.ones_like(out), ad, bd, *ARGS, precision="tf32")
+        flow = torch.zeros(2, 24, 32, 2, device=dev)
+        w = fn2.flow_warp(ad[..., :3].contiguous(), flow)
+        ds = fn2.downsample_multi(torch.randn(2, 64, 64, 2, generator=torch.Generator().manual_seed(1)).to(dev),
+                                  [(4, 4), (8, 8)])
+        torch.cuda.synchronize(dev)
+        res.append([t.cpu() for t in (out, ga, gb, w, *ds)])
+    for x, y in zip(*res):
+        assert torch.equal(x, y)
 
 
 @pytest.mark.parametrize("shape", [
@@ -104,18 +204,20 @@ def test_unsupported_precision_is_an_error_not_a_fallback():
     (75, 24, 32, 32),    # 300 pair tiles on 74 pairs: 4 rounds + a split tail of 4 tiles
     (37, 16, 32, 128),   # exactly two rounds, no tail (C a power of two: the 1/C scaling stays exact)
     (3, 48, 64, 256),    # fewer pair tiles than resident pairs (one tile each)
+    (2, 20, 140, 32),    # wide classes: three column tiles, two 32-column b blocks per group of b-rows
 ])
-def test_persistent_pair_forward_is_exact_on_integer_inputs(shape):
+@pytest.mark.parametrize("precision", ["tf32", "tf32x3"])
+def test_persistent_pair_forward_is_exact_on_integer_inputs(shape, precision):
     """The persistent CTA-pair forward walks a work list with running barrier phases; integer inputs make every sum
     exact, so any tile taken twice, skipped, or computed against a stale a tile shows as a wrong integer."""
     N, H, W, C = shape
     g = torch.Generator().manual_seed(sum(shape))
     a = torch.randint(-3, 4, shape, generator=g).float()
     b = torch.randint(-3, 4, shape, generator=g).float()
-    out = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    out = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision=precision)
     want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
     np.testing.assert_array_equal(out.cpu().numpy().astype(np.float64), want)
-    out2 = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    out2 = fn2.correlation(a.cuda(), b.cuda(), *ARGS, precision=precision)
     assert torch.equal(out, out2)
 
 
@@ -125,7 +227,8 @@ def test_persistent_pair_forward_is_exact_on_integer_inputs(shape):
     (6, 20, 140, 32),    # wide classes: three column tiles, two 32-pixel items per source row
     (3, 48, 64, 256),    # fewer tiles than CTAs (one tile each)
 ])
-def test_persistent_backward_is_exact_on_integer_inputs(shape):
+@pytest.mark.parametrize("precision", ["tf32", "tf32x3"])
+def test_persistent_backward_is_exact_on_integer_inputs(shape, precision):
     """The persistent backward kernel carries its stage ring, row barriers and accumulator from tile to tile; integer
     inputs make every sum exact (C is a power of two), so a stale G block, an undrained accumulator row or a tile
     taken twice shows as a wrong number."""
@@ -134,9 +237,9 @@ def test_persistent_backward_is_exact_on_integer_inputs(shape):
     a = torch.randint(-3, 4, shape, generator=g).float()
     b = torch.randint(-3, 4, shape, generator=g).float()
     gr = torch.randint(-3, 4, (N, H, W, 441), generator=g).float()
-    ga, gb = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    ga, gb = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision=precision)
     wa, wb = o.c_correlation_grad(gr.numpy(), a.numpy(), b.numpy(), *ARGS, f64=True)
     np.testing.assert_array_equal(ga.cpu().numpy().astype(np.float64), wa)
     np.testing.assert_array_equal(gb.cpu().numpy().astype(np.float64), wb)
-    ga2, gb2 = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision="tf32")
+    ga2, gb2 = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision=precision)
     assert torch.equal(ga, ga2) and torch.equal(gb, gb2)

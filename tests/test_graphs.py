@@ -107,8 +107,17 @@ def test_loss_matches_a_direct_restatement():
         p = preds["predict_flow%d" % k]
         d = ops.downsample(gt * 0.05, [p.shape[1], p.shape[2]])
         want += wgt * float(torch.sqrt(((p - d) ** 2).sum(3)).sum() / 2)
+    want /= 5       # tf.losses.compute_weighted_loss, default reduction SUM_BY_NONZERO_WEIGHTS (flownet_c.py:163)
     assert abs(float(total) - want) < 1e-4 * max(1.0, abs(want))
     assert len(parts) == 5
+
+
+def test_weighted_loss_is_pinned_to_a_hand_computed_compute_weighted_loss():
+    """tf.losses.compute_weighted_loss(losses, weights) = sum(losses * weights) / count(weights != 0): for losses
+    10, 20, 30, 40, 50 and the FlowNet weights that is (3.2 + 1.6 + 0.6 + 0.4 + 0.25) / 5 = 1.21, not 6.05."""
+    losses = [torch.tensor(v) for v in (10.0, 20.0, 30.0, 40.0, 50.0)]
+    assert abs(float(G.weighted_loss(losses, G.LOSS_WEIGHTS)) - 1.21) < 1e-6
+    assert abs(float(G.weighted_loss(losses, (0.5, 0.0, 0.0, 0.0, 0.25))) - (5.0 + 12.5) / 2) < 1e-6   # zero weights do not count
 
 
 def test_training_step_sends_gradients_through_the_correlation():
