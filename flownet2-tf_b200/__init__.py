@@ -11,9 +11,9 @@ tensor raises.
 """
 from .correlation import correlation, correlation_grad, correlation_leaky_concat  # noqa: F401
 from .flow_warp import flow_warp, flow_warp_grad, flow_warp_error  # noqa: F401
-from .downsample import downsample, downsample_multi  # noqa: F401
+from .downsample import downsample, downsample_multi, multiscale_epe  # noqa: F401
 from .flo import read_flo, write_flo  # noqa: F401
 from . import _lib  # noqa: F401
 
 __all__ = ["correlation", "correlation_grad", "flow_warp", "flow_warp_grad", "downsample",
-           "downsample_multi", "correlation_leaky_concat", "flow_warp_error", "read_flo", "write_flo"]
+           "downsample_multi", "multiscale_epe", "correlation_leaky_concat", "flow_warp_error", "read_flo", "write_flo"]

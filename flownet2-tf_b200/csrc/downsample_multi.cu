@@ -1,230 +1,317 @@
-// downsample_multi.cu -- all the loss scales of one tensor in ONE pass over the input.
+// downsample_multi.cu -- all the loss scales of one tensor in ONE pass over the input, and (optionally) the loss terms
+// that consume them.
 //
-// The reference's loss (flownet_c.py:135-160, flownet_s.py / flownet_sd.py likewise) calls downsample(gt_flow, size)
-// five times on the same [N,384,512,2] tensor; every call re-reads the whole input.  Each scale is the NaN-aware
-// triangular-weighted average of downsample_kernel_gpu.cu.cc:35-76, and every scale is
-// computed DIRECTLY from the input (the scale centres are not nested, so no scale can be derived from another).
+// The reference's loss (flownet_c.py:127-166, flownet_s.py / flownet_sd.py likewise) scales the ground-truth flow
+// (flow * 0.05), calls downsample(flow, size) five times on the same [N,384,512,2] tensor -- every call re-reading the
+// whole input -- and reduces each scale against a prediction with average_endpoint_error (utils.py:209-224).  Each
+// scale is the NaN-aware triangular-weighted average of downsample_kernel_gpu.cu.cc:35-76, and
+// every scale is computed DIRECTLY from the input (the scale centres are not nested).
 //
-// Work split: a thread-block cluster of up to 16 CTAs (8 once the batch fills the chip) owns one image; rank r walks the input rows
-// [r*chunk, (r+1)*chunk).  Thread x owns PX adjacent input columns and reads each of its rows exactly once (coalesced
-// 16-byte loads, U rows in flight).  The weight is separable, w = wx(x) * wy(y): an input row feeds at most two output
-// rows of every scale (the last centre at or above it, and the next one), so the thread keeps, per scale, the vertical
-// value / weight sums of those two live output rows in registers -- 2 FMAs per input float, scale and live row.  When
-// the walk passes the centre of the next output row of a scale (the same row index for every thread: a uniform
-// branch), the finished row is parked in shared memory and summed horizontally by sub-warp groups in a fixed order
-// into the rank's partial-result table.  After the walk the ranks add their partial rows through distributed shared
-// memory in rank order (deterministic) and apply the NaN rule (:72-76).  Every input byte is read once from DRAM;
-// all scales together write < 2 % of that.
+// Three launches, no atomics on data, a fixed summation order that does not depend on the batch size:
+//   0. ms_tables_kernel   -- the weight tables, which depend only on the shapes: per (scale, input row) the output row
+//      dlo below it and its two vertical weights, the same per input column, the column ranges of every output column,
+//      the total weights, and which tiles feed which output.  One thread (or warp) per entry; the IEEE divisions of the
+//      reference's formula are done once per launch here, not once per CTA.
+//   1. ms_band_kernel     -- grid (row bands of 16 input rows) x (images): short CTAs, many waves.  A thread owns 4
+//      adjacent floats of a row (16-byte loads, 4 rows in flight) and reads each exactly once.  The weight is separable,
+//      w = wx(x) * wy(y), and an input row feeds at most two output rows of every scale (the last centre at or above
+//      it, and the next one), so the thread keeps, per scale, the vertical value sums of those two live output rows in
+//      registers (the NaN-weight sums live in thread-private shared-memory slots that are only touched once a warp
+//      has met a NaN: none of that work is done for NaN-free input).  When the walk passes the centre of the next output row of a scale (a block-uniform
+//      branch) the finished row is reduced horizontally BY EACH WARP ON ITS OWN: the lanes park their x-weighted column
+//      sums in the warp's private shared-memory strip, and small lane groups add up the strip's share of every output
+//      column it touches in a fixed order.  No block barrier, no cluster: warps never wait for each other.  The warp's
+//      partial rows go to the caller's workspace (they stay in L2).
+//   2. ms_combine_kernel  -- one thread per output pixel adds the partials of the (band, warp) tiles that feed it, in
+//      tile order, applies the NaN rule (:72-76) and writes the downsampled value; when predictions are given it also
+//      forms the end-point error sqrt(sum_c (pred - down)^2), the unit residual (pred - down) / epe that the loss
+//      gradient needs, and the per-scale sums (block tree, then one ordered pass by the last block to finish).
+// NaN samples: the reference keeps accum_weight (non-NaN samples) and accum_nan; here the NaN weight is accumulated
+// itself (exactly zero when there is no NaN) and accum_weight = total weight - accum_nan, the total being a table.
 #include <cstdlib>
-#include <cooperative_groups.h>
-#include <mutex>
 #include "fn2_common.cuh"
 #include "fn2_downsample.cuh"
 
 namespace fn2 {
 namespace {
 
-namespace cg = cooperative_groups;
-
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int MS = 5;          // scales per launch (the reference's losses use five, flownet_c.py:135-160)
-constexpr int MAX_RANKS = 16;  // largest cluster (non-portable size, opted into per kernel); 8 is the portable fallback
+constexpr int MS = 5;     // scales per launch (the reference's losses use five, flownet_c.py:135-160)
+constexpr int RB = 16;    // input rows per band
+constexpr int U = 4;      // rows in flight per thread
+constexpr int CB = 256;   // threads of the combine kernel
 
-struct MsParams {
-  int N, iH, iW, ns, chunk;
-  int oH[MS], oW[MS], maxRows[MS];
-  int csOff[MS], trOff[MS], ptOff[MS];   // offsets of each scale's column-start / row-total / partial tables
-  int csTotal, trTotal, ptTotal;
-  float hs[MS], ws[MS];
-  float* out[MS];
+// Offsets (4-byte words) of the per-scale tables inside the workspace.
+struct MsTables {
+  int rowW[MS];    // [iH] float2: weight of input row y towards output rows dlo(y), dlo(y) + 1
+  int rowD[MS];    // [iH] int: dlo(y)
+  int colW[MS];    // [iW] float2: the same along x
+  int colD[MS];    // [iW] int
+  int colS[MS];    // [oW + 1] int: first input column whose nearest-left output column is dx
+  int totX[MS];    // [oW] float: sum of the x-weights of output column dx
+  int totY[MS];    // [oH] float
+  int bandR[MS];   // [oH] int2: first / last band that feeds output row dy
+  int warpR[MS];   // [oW] int2: first / last warp strip that feeds output column dx
+  int words;       // size of the table area
 };
 
-// shared-memory words (4 bytes each) of one CTA
-__host__ __device__ inline size_t ms_smem_words(int chunk, int ncols, int nv, int csTotal, int trTotal, int ptTotal) {
-  return (size_t)3 * MS * chunk + chunk      // rowA, rowB, rowD, flush mask
-         + (size_t)2 * MS * ncols            // wA, wB
-         + csTotal + trTotal                 // colStart, totRow
-         + (size_t)nv * ncols                // parked row
-         + ptTotal;                          // partial results
+struct MsParams {
+  int N, iH, iW, ns;
+  int nbands, nwarps, pxw;        // bands per image, warp strips per row, input pixels per warp strip
+  int oH[MS], oW[MS];
+  int maxRows[MS], maxCols[MS];   // output rows a band / output columns a warp strip can touch
+  int J[MS];                      // lanes that share one output column in the horizontal pass
+  int pOff[MS], pTile;            // partial entries: offset of scale s inside a tile, entries per tile
+  int blkOff[MS + 1];             // combine kernel: first block of scale s within an image
+  float hs[MS], ws[MS];
+  float in_scale;                 // samples are multiplied by this on load (the loss's flow * 0.05), 1 = none
+  MsTables t;
+  float* out[MS];                 // downsampled tensors (may be null when only the loss terms are wanted)
+  const float* pred[MS];          // predictions to compare with (null: plain downsample)
+  float* dir[MS];                 // (pred - down) / epe per element (may be null)
+  float* epe;                     // [ns] per-scale sum of end-point errors, divided by N (null without pred)
+  size_t ctrlOff, partOff;        // byte offsets in the workspace: control block (ticket + block sums), partials
+};
+
+// Shared-memory layout of the band kernel (bytes, every area 16-byte aligned); used by the host for the launch size.
+struct BandSmem {
+  size_t rowW, rowD, fmask, wcol, colW, colS, stage, nanw, total;
+};
+__host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
+__host__ __device__ inline BandSmem band_smem_layout(int nwarps, int px, int nv, int cswords) {
+  BandSmem L;
+  size_t o = 0;
+  L.rowW = o; o = up16(o + (size_t)MS * RB * 8);
+  L.rowD = o; o = up16(o + (size_t)MS * RB * 4);
+  L.fmask = o; o = up16(o + (size_t)RB * 4);
+  L.wcol = o; o = up16(o + (size_t)nwarps * MS * 2 * 4);
+  L.colW = o; o = up16(o + (size_t)MS * nwarps * 32 * px * 8);
+  L.colS = o; o = up16(o + (size_t)cswords * 4);
+  L.stage = o; o = up16(o + (size_t)nwarps * 2 * (32 * px) * nv * 4);
+  L.nanw = o; o = up16(o + (size_t)MS * 2 * nwarps * 32 * 16);
+  L.total = o;
+  return L;
 }
 
-#ifdef FN2_TIMELINE
-__device__ long long g_tld[16];
-#define TLD(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tld[i] = clock64(); } while (0)
-#else
-#define TLD(i) do {} while (0)
-#endif
-
-template <int CT, int PX, int U>
-__global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const float* __restrict__ in) {
-  constexpr int NV = 2 * CT;                  // per column and output row: value and weight sums per channel
-  constexpr int NF = CT * PX;                 // floats per thread and row
-  extern __shared__ float sm[];
-  __shared__ int dF[MAX_RANKS][MS], dL[MAX_RANKS][MS];   // output rows [dF, dL] of scale s that rank r feeds
-  cg::cluster_group cluster = cg::this_cluster();
-  const int rs = (int)cluster.num_blocks();
-  const int rank = (int)cluster.block_rank();
-  const int n = blockIdx.x / rs;
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  const int ncols = nthr * PX;
-  const int chunk = p.chunk;
-  const int yb = rank * chunk, ye = min(p.iH - 1, yb + chunk - 1);
-
-  float* rowA = sm;                                        // [MS][chunk] weight of row i towards output row dlo
-  float* rowB = rowA + (size_t)MS * chunk;                 // [MS][chunk] ... towards dlo + 1
-  int* rowD = reinterpret_cast<int*>(rowB + (size_t)MS * chunk);   // [MS][chunk] dlo
-  int* fmask = rowD + (size_t)MS * chunk;                  // [chunk] bit s: scale s finishes an output row before row i
-  float* wA = reinterpret_cast<float*>(fmask + chunk);     // [MS][ncols] x-weight towards output column dxl(x)
-  float* wB = wA + (size_t)MS * ncols;                     // [MS][ncols] ... towards dxl(x) + 1
-  int* colStart = reinterpret_cast<int*>(wB + (size_t)MS * ncols);   // per scale [oW + 1]
-  float* totRow = reinterpret_cast<float*>(colStart + p.csTotal);    // per scale [maxRows] total vertical weight
-  float* rowbuf = totRow + p.trTotal;                      // [NV][ncols] the parked output row
-  float* part = rowbuf + (size_t)NV * ncols;               // per scale [maxRows][oW][NV + 1]
-
-  TLD(0);
-  // ---- tables ----
-  for (int idx = tid; idx < MS * chunk; idx += nthr) {
-    const int s = idx / chunk, i = idx - s * chunk, y = yb + i;
-    float a = 0.f, b = 0.f;
-    int d = 0;
-    if (s < p.ns && y <= ye) {
-      d = last_centre_le(y, p.hs[s], p.oH[s], p.iH);
-      a = tri((float)y, src_pos(d, p.oH[s] - 1, p.iH - 1), p.hs[s]);
-      b = d + 1 < p.oH[s] ? tri((float)y, src_pos(d + 1, p.oH[s] - 1, p.iH - 1), p.hs[s]) : 0.f;
-    }
-    rowA[idx] = a; rowB[idx] = b; rowD[idx] = d;
-  }
-  for (int idx = tid; idx < MAX_RANKS * MS; idx += nthr) {
-    const int r = idx / MS, s = idx - r * MS;
-    const int ybr = r * chunk, yer = min(p.iH - 1, ybr + chunk - 1);
-    int f = 1, l = 0;
-    if (r < rs && s < p.ns && ybr <= yer) {
-      f = last_centre_le(ybr, p.hs[s], p.oH[s], p.iH);
-      l = min(p.oH[s] - 1, last_centre_le(yer, p.hs[s], p.oH[s], p.iH) + 1);
-      l = min(l, f + p.maxRows[s] - 1);
-    }
-    dF[r][s] = f; dL[r][s] = l;
-  }
+// ---------------------------------------------------------------------------------------------------- tables
+__global__ void ms_tables_kernel(MsParams p, float* __restrict__ ws) {
+  int* wi = reinterpret_cast<int*>(ws);
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int gthreads = gridDim.x * blockDim.x;
+  const int gwarp = gtid >> 5, gwarps = gthreads >> 5, lane = threadIdx.x & 31;
+  if (gtid == 0) *reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + p.ctrlOff) = 0u;   // combine ticket
   for (int s = 0; s < p.ns; ++s) {
-    const int oW = p.oW[s];
-    int* cs = colStart + p.csOff[s];
-    for (int dx = tid; dx <= oW; dx += nthr)
-      cs[dx] = dx == 0 ? 0 : (dx == oW ? p.iW : (int)ceilf(src_pos(dx, oW - 1, p.iW - 1)));
-    for (int x = tid; x < ncols; x += nthr) {
-      const bool colok = x < p.iW;
-      const int dxl = last_centre_le(min(x, p.iW - 1), p.ws[s], oW, p.iW);
-      wA[s * ncols + x] = colok ? tri((float)x, src_pos(dxl, oW - 1, p.iW - 1), p.ws[s]) : 0.f;
-      wB[s * ncols + x] = (colok && dxl + 1 < oW) ? tri((float)x, src_pos(dxl + 1, oW - 1, p.iW - 1), p.ws[s]) : 0.f;
+    const int oH = p.oH[s], oW = p.oW[s];
+    const float hs = p.hs[s], wsc = p.ws[s];
+    // one thread per input row / input column
+    for (int y = gtid; y < p.iH; y += gthreads) {
+      const int d = last_centre_le(y, hs, oH, p.iH);
+      const float a = tri((float)y, src_pos(d, oH - 1, p.iH - 1), hs);
+      const float b = d + 1 < oH ? tri((float)y, src_pos(d + 1, oH - 1, p.iH - 1), hs) : 0.f;
+      reinterpret_cast<float2*>(ws + p.t.rowW[s])[y] = make_float2(a, b);
+      wi[p.t.rowD[s] + y] = d;
+    }
+    for (int x = gtid; x < p.iW; x += gthreads) {
+      const int d = last_centre_le(x, wsc, oW, p.iW);
+      const float a = tri((float)x, src_pos(d, oW - 1, p.iW - 1), wsc);
+      const float b = d + 1 < oW ? tri((float)x, src_pos(d + 1, oW - 1, p.iW - 1), wsc) : 0.f;
+      reinterpret_cast<float2*>(ws + p.t.colW[s])[x] = make_float2(a, b);
+      wi[p.t.colD[s] + x] = d;
+    }
+    // one thread per output row / column: ranges
+    for (int dx = gtid; dx <= oW; dx += gthreads) {
+      wi[p.t.colS[s] + dx] = dx == 0 ? 0 : (dx == oW ? p.iW : (int)ceilf(src_pos(dx, oW - 1, p.iW - 1)));
+      if (dx < oW) {
+        // strip w feeds dx iff dlo(first px) <= dx and dlo(last px) >= dx - 1   (dlo(x) >= d  <=>  x >= centre(d))
+        const int xlo = dx >= 2 ? (int)ceilf(src_pos(dx - 1, oW - 1, p.iW - 1)) : 0;
+        const int xhi = dx + 1 < oW ? (int)ceilf(src_pos(dx + 1, oW - 1, p.iW - 1)) - 1 : p.iW - 1;
+        reinterpret_cast<int2*>(wi + p.t.warpR[s])[dx] =
+            make_int2(min(xlo, p.iW - 1) / p.pxw, min(max(xhi, 0), p.iW - 1) / p.pxw);
+      }
+    }
+    for (int dy = gtid; dy < oH; dy += gthreads) {
+      const int ylo = dy >= 2 ? (int)ceilf(src_pos(dy - 1, oH - 1, p.iH - 1)) : 0;
+      const int yhi = dy + 1 < oH ? (int)ceilf(src_pos(dy + 1, oH - 1, p.iH - 1)) - 1 : p.iH - 1;
+      reinterpret_cast<int2*>(wi + p.t.bandR[s])[dy] =
+          make_int2(min(ylo, p.iH - 1) / RB, min(max(yhi, 0), p.iH - 1) / RB);
+    }
+    // one warp per output row / column: total weights (lane-strided, then a fixed tree)
+    for (int e = gwarp; e < oH + oW; e += gwarps) {
+      const bool isx = e >= oH;
+      const int d = isx ? e - oH : e;
+      const int on = isx ? oW : oH, in_ = isx ? p.iW : p.iH;
+      const float sc = isx ? wsc : hs;
+      const float c = src_pos(d, on - 1, in_ - 1);
+      const int lo = max(0, (int)floorf(c - sc)), hi = min(in_ - 1, (int)ceilf(c + sc));
+      float t = 0.f;
+      for (int i = lo + lane; i <= hi; i += 32) t += tri((float)i, c, sc);
+      for (int off = 16; off >= 1; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+      if (lane == 0) ws[(isx ? p.t.totX[s] : p.t.totY[s]) + d] = t;
     }
   }
-  for (int i = tid; i < p.ptTotal; i += nthr) part[i] = 0.f;
+}
+
+template <int NV>
+__device__ __forceinline__ void add_entry(float (&acc)[NV], const float* e) {
+  if constexpr (NV == 4) {
+    const float4 t = *reinterpret_cast<const float4*>(e);
+    acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+  } else {
+    const float2 t = *reinterpret_cast<const float2*>(e);
+    acc[0] += t.x; acc[1] += t.y;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------- band walk
+// CT channels; a thread owns PX = 4 / CT adjacent pixels (one float4 per row).
+template <int CT>
+__global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float* __restrict__ in,
+                                                         float* __restrict__ ws) {
+  constexpr int PX = 4 / CT;
+  constexpr int NV = 2 * CT;                    // per pixel: value and NaN-weight sums per channel
+  extern __shared__ __align__(16) uint8_t sm[];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int band = blockIdx.x, n = blockIdx.y;
+  const int yb = band * RB, ye = min(p.iH - 1, yb + RB - 1);
+  const int nrows = ye - yb + 1;
+  const int ncols = nthr * PX;
+  const int pxw = 32 * PX;
+  const int* wsi = reinterpret_cast<const int*>(ws);
+
+  // the colS tables are packed back to back in the workspace and followed by totX[0]
+  const int cswords = p.t.totX[0] - p.t.colS[0];
+  const BandSmem L = band_smem_layout(nthr >> 5, PX, NV, cswords);
+  float2* rowW = reinterpret_cast<float2*>(sm + L.rowW);     // [MS][RB]
+  int* rowD = reinterpret_cast<int*>(sm + L.rowD);           // [MS][RB]
+  int* fmask = reinterpret_cast<int*>(sm + L.fmask);         // [RB] bit s: scale s finishes an output row before row i
+  int* wcol = reinterpret_cast<int*>(sm + L.wcol);           // [nwarps][MS][2] first / last output column of a strip
+  float2* colW = reinterpret_cast<float2*>(sm + L.colW);     // [MS][ncols]
+  int* colS = reinterpret_cast<int*>(sm + L.colS);           // per scale [oW + 1], packed
+  float* stage = reinterpret_cast<float*>(sm + L.stage);     // per warp: strips A and B, [pxw][NV] each
+  float4* nanw = reinterpret_cast<float4*>(sm + L.nanw) + tid;   // [MS][2][nthr]: this thread's NaN-weight sums
+
+  // ---- this band's slice of the tables ----
+  for (int idx = tid; idx < MS * RB; idx += nthr) {
+    const int s = idx / RB, i = idx - s * RB;
+    float2 w = make_float2(0.f, 0.f);
+    int d = 0;
+    if (s < p.ns && i < nrows) {
+      w = reinterpret_cast<const float2*>(ws + p.t.rowW[s])[yb + i];
+      d = wsi[p.t.rowD[s] + yb + i];
+    }
+    rowW[idx] = w; rowD[idx] = d;
+  }
+  for (int idx = tid; idx < MS * ncols; idx += nthr) {
+    const int s = idx / ncols, x = idx - s * ncols;
+    colW[idx] = (s < p.ns && x < p.iW) ? reinterpret_cast<const float2*>(ws + p.t.colW[s])[x] : make_float2(0.f, 0.f);
+  }
+  for (int i = tid; i < cswords; i += nthr) colS[i] = wsi[p.t.colS[0] + i];
+  if (lane < MS) {
+    const int s = lane;
+    const int wx0 = warp * pxw, wx1 = min(wx0 + pxw, p.iW);
+    int cf = 0, cl = -1;
+    if (s < p.ns && wx0 < p.iW) {
+      cf = wsi[p.t.colD[s] + wx0];
+      cl = min(p.oW[s] - 1, wsi[p.t.colD[s] + wx1 - 1] + 1);
+    }
+    wcol[(warp * MS + s) * 2] = cf; wcol[(warp * MS + s) * 2 + 1] = cl;
+  }
   __syncthreads();
-  for (int i = tid; i < chunk; i += nthr) {
+  for (int i = tid; i < RB; i += nthr) {
     int m = 0;
-    if (i > 0 && yb + i <= ye)
-      for (int s = 0; s < p.ns; ++s) m |= (rowD[s * chunk + i] != rowD[s * chunk + i - 1]) ? (1 << s) : 0;
+    if (i > 0 && i < nrows)
+      for (int s = 0; s < p.ns; ++s) m |= (rowD[s * RB + i] != rowD[s * RB + i - 1]) ? (1 << s) : 0;
     fmask[i] = m;
   }
-  for (int idx = tid; idx < p.trTotal; idx += nthr) {   // every (scale, local output row) on its own thread
-      int s = 0;
-      while (s + 1 < p.ns && p.trOff[s + 1] <= idx) ++s;
-      const int dyl = idx - p.trOff[s];
-      const int dy = dF[rank][s] + dyl;
-      float t = 0.f;
-      for (int i = 0; i <= ye - yb; ++i) {
-        const int d = rowD[s * chunk + i];
-        if (d == dy) t += rowA[s * chunk + i];
-        if (d + 1 == dy) t += rowB[s * chunk + i];
-      }
-      totRow[p.trOff[s] + dyl] = t;
-    }
   __syncthreads();
+  // From here on the warps are independent.
 
-  TLD(1);
-  // ---- horizontal pass of the parked row -> partial-result row dy of scale s ----
-  auto horizontal = [&](int s, int dy) {
-    __syncthreads();                                       // the parked row is complete
-    const int dyl = dy - dF[rank][s];
-    const int oW = p.oW[s];
-    if (dyl >= 0 && dyl < p.maxRows[s] && dy < p.oH[s]) {
-      const int* cs = colStart + p.csOff[s];
-      const float* a_ = wA + s * ncols;
-      const float* b_ = wB + s * ncols;
-      int J = 1;
-      while (J < 32 && J * 2 * oW <= nthr) J *= 2;
-      const int j = tid % J;
-      for (int it0 = 0; it0 < oW; it0 += nthr / J) {
-        const int dx = it0 + tid / J;
-        const bool live = dx < oW;
-        float acc[NV];
+  float* stA = stage + (size_t)warp * (2 * pxw * NV);   // [pxw][NV] contributions to column dlo(x)
+  float* stB = stA + pxw * NV;                          // [pxw][NV] ... to column dlo(x) + 1
+  const int wx0 = warp * pxw, wx1 = min(wx0 + pxw, p.iW);
+  float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + p.partOff) +
+                ((size_t)((size_t)n * p.nbands + band) * p.nwarps + warp) * p.pTile * NV;
+
+  // ---- horizontal pass of one finished output row (scale s, live row k of the accumulators) ----
+  bool sawnan = false;                                       // warp-uniform: the NaN-weight slots are in use
+  auto flush = [&](int s, int k, const float (&av)[4], int dy) {
+    if (dy >= p.oH[s]) return;                               // uniform
+    {
+      float an[4] = {0.f, 0.f, 0.f, 0.f};
+      if (sawnan) {
+        const float4 t = nanw[(s * 2 + k) * nthr];
+        an[0] = t.x; an[1] = t.y; an[2] = t.z; an[3] = t.w;
+      }
+      const float2* cw = colW + s * ncols + tid * PX;
 #pragma unroll
-        for (int k = 0; k < NV; ++k) acc[k] = 0.f;
-        float wsum = 0.f;                                  // sum of the x-weights (for the total weight)
-        if (live) {
-          const int c1 = cs[dx], c2 = cs[dx + 1];
-          if (dx > 0)
-            for (int xx = cs[dx - 1] + j; xx < c1; xx += J) {   // columns whose right neighbour is dx
-              const float w = b_[xx];
-              wsum += w;
+      for (int q = 0; q < PX; ++q) {
+        const float2 w = cw[q];
+        float a_[NV], b_[NV];
 #pragma unroll
-              for (int k = 0; k < NV; ++k) acc[k] = fmaf(w, rowbuf[k * ncols + xx], acc[k]);
-            }
-          for (int xx = c1 + j; xx < c2; xx += J) {              // columns whose left neighbour is dx
-            const float w = a_[xx];
-            wsum += w;
-#pragma unroll
-            for (int k = 0; k < NV; ++k) acc[k] = fmaf(w, rowbuf[k * ncols + xx], acc[k]);
-          }
+        for (int c = 0; c < CT; ++c) {
+          a_[c] = w.x * av[q * CT + c]; a_[CT + c] = w.x * an[q * CT + c];
+          b_[c] = w.y * av[q * CT + c]; b_[CT + c] = w.y * an[q * CT + c];
         }
-        for (int off = J >> 1; off >= 1; off >>= 1) {
-          wsum += __shfl_xor_sync(FULL, wsum, off);
-#pragma unroll
-          for (int k = 0; k < NV; ++k) acc[k] += __shfl_xor_sync(FULL, acc[k], off);
-        }
-        if (live && j == 0) {
-          float* pr = part + p.ptOff[s] + ((size_t)dyl * oW + dx) * (NV + 1);
-#pragma unroll
-          for (int k = 0; k < NV; ++k) pr[k] = acc[k];
-          pr[NV] = wsum * totRow[p.trOff[s] + dyl];
+        if constexpr (NV == 4) {
+          *reinterpret_cast<float4*>(stA + (lane * PX + q) * 4) = make_float4(a_[0], a_[1], a_[2], a_[3]);
+          *reinterpret_cast<float4*>(stB + (lane * PX + q) * 4) = make_float4(b_[0], b_[1], b_[2], b_[3]);
+        } else {
+          *reinterpret_cast<float2*>(stA + (lane * PX + q) * 2) = make_float2(a_[0], a_[1]);
+          *reinterpret_cast<float2*>(stB + (lane * PX + q) * 2) = make_float2(b_[0], b_[1]);
         }
       }
     }
-    __syncthreads();                                       // the parked row may be overwritten
+    __syncwarp();
+    const int cf = wcol[(warp * MS + s) * 2], cl = wcol[(warp * MS + s) * 2 + 1];
+    const int J = p.J[s];
+    const int* cs = colS + (p.t.colS[s] - p.t.colS[0]);
+    const int jl = lane & (J - 1);
+    float* prow = part + ((size_t)p.pOff[s] + (size_t)(dy - rowD[s * RB]) * p.maxCols[s]) * NV;
+    for (int j0 = 0; cf + j0 <= cl; j0 += 32 / J) {
+      const int j = j0 + lane / J;
+      const int dx = cf + j;
+      const bool live = dx <= cl;
+      float acc[NV];
+#pragma unroll
+      for (int k = 0; k < NV; ++k) acc[k] = 0.f;
+      if (live) {
+        const int c1 = cs[dx], c2 = cs[dx + 1];
+        if (dx > 0)
+          for (int xx = max(cs[dx - 1], wx0) + jl; xx < min(c1, wx1); xx += J)     // columns whose right neighbour is dx
+            add_entry<NV>(acc, stB + (xx - wx0) * NV);
+        for (int xx = max(c1, wx0) + jl; xx < min(c2, wx1); xx += J)               // columns whose left neighbour is dx
+          add_entry<NV>(acc, stA + (xx - wx0) * NV);
+      }
+      for (int off = J >> 1; off >= 1; off >>= 1) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] += __shfl_xor_sync(FULL, acc[k], off);
+      }
+      if (live && jl == 0) {
+        if constexpr (NV == 4) *reinterpret_cast<float4*>(prow + j * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        else *reinterpret_cast<float2*>(prow + j * 2) = make_float2(acc[0], acc[1]);
+      }
+    }
+    __syncwarp();                                            // the strip may be overwritten
   };
 
   // ---- walk the rows ----
-  float av[MS][2][NF], aw[MS][2][NF];
+  float av[MS][2][4];
 #pragma unroll
   for (int s = 0; s < MS; ++s)
 #pragma unroll
     for (int k = 0; k < 2; ++k)
 #pragma unroll
-      for (int f = 0; f < NF; ++f) av[s][k][f] = aw[s][k][f] = 0.f;
+      for (int f = 0; f < 4; ++f) av[s][k][f] = 0.f;
   const int x0 = tid * PX;
   const float* col = in + ((size_t)n * p.iH * p.iW + (size_t)min(x0, p.iW - PX)) * CT;
+  const float scale = p.in_scale;
 
   for (int y0 = yb; y0 <= ye; y0 += U) {
-    float v[U][NF];
+    float4 v[U];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const float* ps = col + (size_t)min(y0 + u, ye) * p.iW * CT;
-      if constexpr (NF % 4 == 0) {
-#pragma unroll
-        for (int f = 0; f < NF; f += 4) {
-          const float4 t = __ldg(reinterpret_cast<const float4*>(ps + f));
-          v[u][f] = t.x; v[u][f + 1] = t.y; v[u][f + 2] = t.z; v[u][f + 3] = t.w;
-        }
-      } else if constexpr (NF % 2 == 0) {
-#pragma unroll
-        for (int f = 0; f < NF; f += 2) {
-          const float2 t = __ldg(reinterpret_cast<const float2*>(ps + f));
-          v[u][f] = t.x; v[u][f + 1] = t.y;
-        }
-      } else {
-#pragma unroll
-        for (int f = 0; f < NF; ++f) v[u][f] = __ldg(ps + f);
-      }
-    }
+    for (int u = 0; u < U; ++u)
+      v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(y0 + u, ye) * p.iW * CT));
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (y0 + u <= ye) {                                  // uniform
@@ -234,132 +321,164 @@ __global__ void __launch_bounds__(512) downsample_multi_kernel(MsParams p, const
 #pragma unroll
           for (int s = 0; s < MS; ++s)
             if ((m >> s) & 1) {
+              flush(s, 0, av[s][0], rowD[s * RB + i - 1]);
 #pragma unroll
-              for (int q = 0; q < PX; ++q)
-#pragma unroll
-                for (int c = 0; c < CT; ++c) {
-                  rowbuf[c * ncols + x0 + q] = av[s][0][q * CT + c];
-                  rowbuf[(CT + c) * ncols + x0 + q] = aw[s][0][q * CT + c];
-                }
-              horizontal(s, rowD[s * chunk + i - 1]);
-#pragma unroll
-              for (int f = 0; f < NF; ++f) {
-                av[s][0][f] = av[s][1][f]; aw[s][0][f] = aw[s][1][f];
-                av[s][1][f] = aw[s][1][f] = 0.f;
+              for (int f = 0; f < 4; ++f) { av[s][0][f] = av[s][1][f]; av[s][1][f] = 0.f; }
+              if (sawnan) {
+                nanw[(s * 2) * nthr] = nanw[(s * 2 + 1) * nthr];
+                nanw[(s * 2 + 1) * nthr] = make_float4(0.f, 0.f, 0.f, 0.f);
               }
             }
         }
-        float sv[NF], ok[NF];
+        // flow * in_scale is a rounded fp32 product, as if the scaled tensor had been materialised (flownet_c.py:128)
+        const float x[4] = {__fmul_rn(v[u].x, scale), __fmul_rn(v[u].y, scale), __fmul_rn(v[u].z, scale),
+                            __fmul_rn(v[u].w, scale)};
+        float sv[4];
+        bool anynan = false;
 #pragma unroll
-        for (int f = 0; f < NF; ++f) {                     // NaN samples only count in the total weight (:61-65)
-          const bool fin = v[u][f] == v[u][f];
-          sv[f] = fin ? v[u][f] : 0.f;
-          ok[f] = fin ? 1.f : 0.f;
+        for (int f = 0; f < 4; ++f) {                      // NaN samples only count in the NaN weight (:61-65)
+          const bool fin = x[f] == x[f];
+          sv[f] = fin ? x[f] : 0.f;
+          anynan |= !fin;
         }
 #pragma unroll
         for (int s = 0; s < MS; ++s) {
-          const float wa = rowA[s * chunk + i], wb = rowB[s * chunk + i];
+          const float2 w = rowW[s * RB + i];
 #pragma unroll
-          for (int f = 0; f < NF; ++f) {
-            av[s][0][f] = fmaf(sv[f], wa, av[s][0][f]); aw[s][0][f] = fmaf(ok[f], wa, aw[s][0][f]);
-            av[s][1][f] = fmaf(sv[f], wb, av[s][1][f]); aw[s][1][f] = fmaf(ok[f], wb, aw[s][1][f]);
+          for (int f = 0; f < 4; ++f) {
+            av[s][0][f] = fmaf(sv[f], w.x, av[s][0][f]);
+            av[s][1][f] = fmaf(sv[f], w.y, av[s][1][f]);
+          }
+        }
+        if (__any_sync(FULL, anynan)) {                    // warp-uniform and rare: NaN weights, in the shared slots
+          if (!sawnan) {
+            sawnan = true;
+            for (int e = 0; e < MS * 2; ++e) nanw[e * nthr] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const float4 nn = make_float4(x[0] == x[0] ? 0.f : 1.f, x[1] == x[1] ? 0.f : 1.f, x[2] == x[2] ? 0.f : 1.f,
+                                        x[3] == x[3] ? 0.f : 1.f);
+          for (int s = 0; s < p.ns; ++s) {
+            const float2 w = rowW[s * RB + i];
+            float4 a = nanw[(s * 2) * nthr], b = nanw[(s * 2 + 1) * nthr];
+            a.x = fmaf(nn.x, w.x, a.x); a.y = fmaf(nn.y, w.x, a.y); a.z = fmaf(nn.z, w.x, a.z); a.w = fmaf(nn.w, w.x, a.w);
+            b.x = fmaf(nn.x, w.y, b.x); b.y = fmaf(nn.y, w.y, b.y); b.z = fmaf(nn.z, w.y, b.z); b.w = fmaf(nn.w, w.y, b.w);
+            nanw[(s * 2) * nthr] = a; nanw[(s * 2 + 1) * nthr] = b;
           }
         }
       }
     }
   }
-  TLD(2);
-  if (yb <= ye) {
 #pragma unroll
-    for (int s = 0; s < MS; ++s)
-      if (s < p.ns) {
-        const int cur = rowD[s * chunk + (ye - yb)];
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-#pragma unroll
-          for (int q = 0; q < PX; ++q)
-#pragma unroll
-            for (int c = 0; c < CT; ++c) {
-              rowbuf[c * ncols + x0 + q] = av[s][k][q * CT + c];
-              rowbuf[(CT + c) * ncols + x0 + q] = aw[s][k][q * CT + c];
-            }
-          horizontal(s, cur + k);
-        }
-      }
-  }
+  for (int s = 0; s < MS; ++s)
+    if (s < p.ns) {
+      const int cur = rowD[s * RB + nrows - 1];
+      flush(s, 0, av[s][0], cur);
+      flush(s, 1, av[s][1], cur + 1);
+    }
+}
 
-  TLD(3);
-  // ---- combine the ranks' partial rows in rank order and finish (:72-76) ----
-  cluster.sync();
-  TLD(4);
-  for (int s = 0; s < p.ns; ++s) {
-    const int oW = p.oW[s];
-    const int total = p.oH[s] * oW * CT;
-    float* o = p.out[s] + (size_t)n * total;
-    for (int idx = rank * nthr + tid; idx < total; idx += rs * nthr) {
-      const int c = idx % CT, item = idx / CT;
-      const int dy = item / oW, dx = item - dy * oW;
-      float v_ = 0.f, w_ = 0.f, t_ = 0.f;
-      for (int r = 0; r < rs; ++r) {
-        if (dy < dF[r][s] || dy > dL[r][s]) continue;
-        const float* rp = cluster.map_shared_rank(part, r) + p.ptOff[s] + ((size_t)(dy - dF[r][s]) * oW + dx) * (NV + 1);
-        v_ += rp[c]; w_ += rp[CT + c]; t_ += rp[NV];
+// --------------------------------------------------------------------------------------------------- combine
+template <int CT>
+__global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __restrict__ ws) {
+  constexpr int NV = 2 * CT;
+  __shared__ float red[CB / 32];
+  __shared__ bool lastBlock;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bpi = p.blkOff[p.ns];
+  const int n = blockIdx.x / bpi, rb = blockIdx.x - n * bpi;
+  int s = 0;
+  while (s + 1 < p.ns && p.blkOff[s + 1] <= rb) ++s;
+  const int oH = p.oH[s], oW = p.oW[s];
+  const int idx = (rb - p.blkOff[s]) * CB + tid;
+  const bool live = idx < oH * oW;
+  const int* wsi = reinterpret_cast<const int*>(ws);
+  const float* parts = reinterpret_cast<const float*>(reinterpret_cast<const char*>(ws) + p.partOff);
+  float epe = 0.f;
+  if (live) {
+    const int dy = idx / oW, dx = idx - dy * oW;
+    const int2 br = reinterpret_cast<const int2*>(wsi + p.t.bandR[s])[dy];
+    const int2 wr = reinterpret_cast<const int2*>(wsi + p.t.warpR[s])[dx];
+    float acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) acc[k] = 0.f;
+    for (int b = br.x; b <= br.y; ++b) {
+      const int slot = dy - wsi[p.t.rowD[s] + b * RB];
+      for (int w = wr.x; w <= wr.y; ++w) {
+        const int j = dx - wsi[p.t.colD[s] + w * p.pxw];
+        const float* e = parts + ((((size_t)n * p.nbands + b) * p.nwarps + w) * p.pTile + p.pOff[s] +
+                                  (size_t)slot * p.maxCols[s] + j) * NV;
+        add_entry<NV>(acc, e);
       }
-      const float n_ = t_ - w_;                            // weight of the NaN samples (accum_nan)
-      o[idx] = (n_ / w_ > 0.5f) ? nan_f() : v_ / w_;
+    }
+    const float tot = ws[p.t.totY[s] + dy] * ws[p.t.totX[s] + dx];
+    const size_t o = (((size_t)n * oH + dy) * oW + dx) * CT;
+    float e2 = 0.f, diff[CT];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+      const float nanw = acc[CT + c];                        // accum_nan
+      const float wgt = tot - nanw;                          // accum_weight: the samples that are not NaN
+      const float r = (nanw / wgt > 0.5f) ? nan_f() : acc[c] / wgt;   // :72-76
+      if (p.out[s]) p.out[s][o + c] = r;
+      if (p.pred[s]) {
+        diff[c] = p.pred[s][o + c] - r;
+        e2 = fmaf(diff[c], diff[c], e2);
+      }
+    }
+    if (p.pred[s]) {
+      epe = sqrtf(e2);                                       // utils.py:219-223
+      if (p.dir[s]) {
+#pragma unroll
+        for (int c = 0; c < CT; ++c) p.dir[s][o + c] = diff[c] / epe;   // 0/0 = NaN, as the gradient of sqrt at 0
+      }
     }
   }
-  TLD(5);
-  cluster.sync();   // keep this CTA's shared memory alive until every rank has read it
-  TLD(6);
-}
-
-template <int CT, int PX, int U>
-int launch_multi(const MsParams& p, int rs, int nthr, const float* in, cudaStream_t st) {
-  auto kern = downsample_multi_kernel<CT, PX, U>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (attr_err == cudaSuccess) attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-  });
-  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); return FN2_E_CUDA; }
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)((long long)rs * p.N));
-  cfg.blockDim = dim3((unsigned)nthr);
-  cfg.dynamicSmemBytes = ms_smem_words(p.chunk, nthr * PX, 2 * CT, p.csTotal, p.trTotal, p.ptTotal) * sizeof(float);
-  cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = (unsigned)rs;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p, in);
-  if (e != cudaSuccess) {
-    (void)cudaGetLastError();
-    if (rs > 8) return 2;   // a 16-CTA cluster does not fit this device / partition: the caller retries with 8
-    note_cuda_error(e);
-    return FN2_E_CUDA;
+  if (p.epe == nullptr) return;                              // uniform: plain downsample
+  // ---- per-scale sums: block tree, then the last block to finish adds the block sums in block order ----
+  for (int off = 16; off >= 1; off >>= 1) epe += __shfl_xor_sync(FULL, epe, off);
+  if (lane == 0) red[warp] = epe;
+  __syncthreads();
+  char* ctrl = reinterpret_cast<char*>(ws) + p.ctrlOff;
+  unsigned* ticket = reinterpret_cast<unsigned*>(ctrl);
+  float* bsum = reinterpret_cast<float*>(ctrl + 16);
+  if (tid == 0) {
+    float t = 0.f;
+    for (int i = 0; i < CB / 32; ++i) t += red[i];
+    bsum[blockIdx.x] = t;
+    __threadfence();
+    lastBlock = atomicAdd(ticket, 1u) == gridDim.x - 1;
   }
-  return after_launch();
+  __syncthreads();
+  if (!lastBlock) return;
+  __threadfence();
+  if (warp < p.ns) {                                         // one warp per scale, lane-strided then a fixed tree
+    const int sc = warp;
+    const int nb = p.blkOff[sc + 1] - p.blkOff[sc];
+    float t = 0.f;
+    for (int i = lane; i < p.N * nb; i += 32) t += __ldcg(bsum + (size_t)(i / nb) * bpi + p.blkOff[sc] + i % nb);
+    for (int off = 16; off >= 1; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+    if (lane == 0) p.epe[sc] = t / (float)p.N;              // utils.py:224: reduce_sum(epe) / num_samples
+  }
+  if (tid == 0) *ticket = 0u;
 }
 
-// One fused launch for up to MS scales; returns 1 if this group of scales cannot take the fused kernel.
-int try_fused(const float* in, float* const* outs, const int* out_hw, int ns, int N, int iH, int iW, int C,
-              cudaStream_t st, int max_ranks) {
-  if (C != 1 && C != 2) return 1;
-  const int px = C == 1 ? (iW % 4 == 0 ? 4 : 1) : (iW % 2 == 0 ? 2 : 1);
-  const int nthr = (((iW + px - 1) / px + 31) / 32) * 32;
-  if (nthr > 512 || iW < px) return 1;
-  if ((long long)N * MAX_RANKS > 0x7fffffffLL) return 1;
-  int rs = 1;
-  while (rs < max_ranks && iH >= 32 * rs) rs *= 2;          // >= 16 rows per rank
-  MsParams p = {};
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Fills the shape-dependent part of the parameters; returns false if these scales cannot take the fused kernels.
+bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int C, size_t* ws_bytes,
+             size_t* band_smem) {
+  MsParams& p = *pp;
+  if (C != 1 && C != 2) return false;
+  const int px = 4 / C;
+  if (iW % px != 0 || iW < px) return false;
+  const int nthr = (((iW / px) + 31) / 32) * 32;
+  if (nthr > 512) return false;
+  if (ns < 1 || ns > MS || N > 65535) return false;
   p.N = N; p.iH = iH; p.iW = iW; p.ns = ns;
-  p.chunk = (iH + rs - 1) / rs;
-  int cs = 0, tr = 0, pt = 0;
+  p.nbands = (iH + RB - 1) / RB;
+  p.nwarps = nthr / 32;
+  p.pxw = 32 * px;
+  int words = 0, pt = 0, blk = 0;
+  auto take = [&](int n) { const int at = words; words += (n + 3) / 4 * 4; return at; };   // 16-byte aligned tables
   for (int s = 0; s < ns; ++s) {
     const int oH = out_hw[2 * s], oW = out_hw[2 * s + 1];
     p.oH[s] = oH; p.oW[s] = oW;
@@ -367,53 +486,104 @@ int try_fused(const float* in, float* const* outs, const int* out_hw, int ns, in
     p.hs[s] = (float)(iH - 1) / (float)(oH - 1);
     // centres at least 1.5 input pixels apart: an input row / column then feeds exactly two outputs per scale and
     // the walk never skips an output row, whatever the rounding of the centres
-    if (!(p.hs[s] >= 1.5f) || !(p.ws[s] >= 1.5f) || oW > 1024) return 1;
-    p.maxRows[s] = (int)((float)(p.chunk - 1) / p.hs[s]) + 3;
-    p.csOff[s] = cs; p.trOff[s] = tr; p.ptOff[s] = pt;
-    cs += oW + 1; tr += p.maxRows[s]; pt += p.maxRows[s] * oW * (2 * C + 1);
-    p.out[s] = outs[s];
+    if (!(p.hs[s] >= 1.5f) || !(p.ws[s] >= 1.5f)) return false;
+    p.maxRows[s] = (int)((float)(RB - 1) / p.hs[s]) + 3;
+    p.maxCols[s] = (int)((float)(p.pxw - 1) / p.ws[s]) + 3;
+    int J = 1;
+    while (J < 32 && J * 2 * p.maxCols[s] <= 32) J *= 2;
+    p.J[s] = J;
+    p.pOff[s] = pt;
+    pt += p.maxRows[s] * p.maxCols[s];
+    p.blkOff[s] = blk;
+    blk += (oH * oW + CB - 1) / CB;
   }
-  p.csTotal = cs; p.trTotal = tr; p.ptTotal = pt;
-  if (ms_smem_words(p.chunk, nthr * px, 2 * C, cs, tr, pt) * sizeof(float) > 200 * 1024) return 1;
-  if (C == 2) return px == 2 ? launch_multi<2, 2, 4>(p, rs, nthr, in, st) : launch_multi<2, 1, 4>(p, rs, nthr, in, st);
-  return px == 4 ? launch_multi<1, 4, 4>(p, rs, nthr, in, st) : launch_multi<1, 1, 4>(p, rs, nthr, in, st);
+  for (int s = ns; s < MS; ++s) {   // unused scales: harmless values (their weights are zero, they are never flushed)
+    p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.maxRows[s] = p.maxCols[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
+  }
+  for (int s = ns; s <= MS; ++s) p.blkOff[s] = blk;
+  p.pTile = pt;
+  // table area; the colS tables are packed back to back and followed by totX[0] (the band kernel copies them as one run)
+  for (int s = 0; s < ns; ++s) { p.t.rowW[s] = take(2 * iH); p.t.rowD[s] = take(iH); }
+  for (int s = 0; s < ns; ++s) { p.t.colW[s] = take(2 * iW); p.t.colD[s] = take(iW); }
+  for (int s = 0; s < ns; ++s) { p.t.colS[s] = words; words += p.oW[s] + 1; }
+  words = (words + 3) / 4 * 4;
+  for (int s = 0; s < ns; ++s) p.t.totX[s] = take(p.oW[s]);
+  for (int s = 0; s < ns; ++s) p.t.totY[s] = take(p.oH[s]);
+  for (int s = 0; s < ns; ++s) { p.t.bandR[s] = take(2 * p.oH[s]); p.t.warpR[s] = take(2 * p.oW[s]); }
+  for (int s = ns; s < MS; ++s) {
+    p.t.rowW[s] = p.t.rowD[s] = p.t.colW[s] = p.t.colD[s] = p.t.colS[s] = p.t.totX[s] = p.t.totY[s] = p.t.bandR[s] =
+        p.t.warpR[s] = 0;
+  }
+  p.t.words = words;
+  const long long nblocks = (long long)N * blk;
+  if (nblocks > 0x7fffffffLL) return false;
+  p.ctrlOff = align_up((size_t)words * 4, 256);
+  p.partOff = align_up(p.ctrlOff + 16 + (size_t)nblocks * 4, 256);
+  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.nwarps * p.pTile * (2 * C) * sizeof(float);
+  *band_smem = band_smem_layout(p.nwarps, px, 2 * C, p.t.totX[0] - p.t.colS[0]).total;
+  return *band_smem <= 160 * 1024;
+}
+
+template <int CT>
+int ms_launch(const MsParams& p, size_t band_smem, const float* in, void* ws, cudaStream_t st) {
+  static PerDeviceOnce once;   // per template instantiation; function attributes are per device
+  const cudaError_t attr_err = per_device_once(once, [] {
+    return cudaFuncSetAttribute(ms_band_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+  });
+  if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  float* w = static_cast<float*>(ws);
+  ms_tables_kernel<<<16, 256, 0, st>>>(p, w);
+  int rc = after_launch();
+  if (rc != FN2_OK) return rc;
+  ms_band_kernel<CT><<<dim3((unsigned)p.nbands, (unsigned)p.N), p.nwarps * 32, band_smem, st>>>(p, in, w);
+  rc = after_launch();
+  if (rc != FN2_OK) return rc;
+  ms_combine_kernel<CT><<<(unsigned)(p.N * p.blkOff[p.ns]), CB, 0, st>>>(p, w);
+  return after_launch();
 }
 
 }  // namespace
 
-#ifdef FN2_TIMELINE
-extern "C" __attribute__((visibility("default"))) int fn2_debug_timeline_ds(long long* host_out) {
-  return (int)cudaMemcpyFromSymbol(host_out, g_tld, sizeof(long long) * 16);
-}
-#endif
-
-int downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
-                             int iW, int C, cudaStream_t st) {
+size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int iH, int iW, int C) {
+  size_t best = 0;
   for (int s0 = 0; s0 < num_scales; s0 += MS) {
     const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
-    // 16-CTA clusters only up to ~1.3 CTAs per SM (measured on B200, 8 -> 16 ranks: N=4 0.079 -> 0.057 ms, N=12
-    // 0.088 -> 0.067, but N=16 0.103 -> 0.134 and N=32 0.107 -> 0.212: 16 co-scheduled CTAs per GPC serialise once
-    // the chip is full)
-    static int big_ok = 1, sms = 0;
-    if (sms == 0) {
-      int dev = 0, v = 0;
-      if (cudaGetDevice(&dev) == cudaSuccess) (void)cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
-      sms = v > 0 ? v : 148;
-    }
-    int max_ranks = (big_ok && (long long)N * MAX_RANKS * 10 <= (long long)sms * 13) ? MAX_RANKS : 8;
-    if (const char* e = getenv("FN2_DS_MAX_RANKS")) max_ranks = min(max(atoi(e), 1), MAX_RANKS);   // A/B switch
-    int rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, max_ranks);
-    if (rc == 2) {   // no room for 16-CTA clusters here: stay with the portable size from now on
-      big_ok = 0;
-      rc = try_fused(in, outs + s0, out_hw + 2 * s0, ns, N, iH, iW, C, st, 8);
-    }
-    if (rc == 1) {   // shapes the fused kernel does not take: one single-scale launch per size (downsample.cu)
+    MsParams p = {};
+    size_t wsb = 0, smem = 0;
+    if (ms_plan(&p, out_hw + 2 * s0, ns, N, iH, iW, C, &wsb, &smem) && wsb > best) best = wsb;
+  }
+  return best;
+}
+
+// predictions / residual_dir / epe_sums may be null (plain multi-scale downsample); outs entries may be null when
+// predictions are given (only the loss terms wanted).
+int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
+                       float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
+                       int C, void* ws, size_t ws_bytes, cudaStream_t st) {
+  for (int s0 = 0; s0 < num_scales; s0 += MS) {
+    const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
+    MsParams p = {};
+    size_t need = 0, smem = 0;
+    if (!ms_plan(&p, out_hw + 2 * s0, ns, N, iH, iW, C, &need, &smem)) {
+      // shapes the fused kernels do not take: one single-scale launch per size (downsample.cu); the loss terms need
+      // the fused path
+      if (preds) return FN2_E_UNSUPPORTED_GEOMETRY;
+      if (in_scale != 1.0f) return FN2_E_UNSUPPORTED_GEOMETRY;
       for (int s = s0; s < s0 + ns; ++s) {
-        rc = downsample_forward(in, outs[s], N, iH, iW, C, out_hw[2 * s], out_hw[2 * s + 1], st);
+        const int rc = downsample_forward(in, outs[s], N, iH, iW, C, out_hw[2 * s], out_hw[2 * s + 1], st);
         if (rc != FN2_OK) return rc;
       }
-      rc = FN2_OK;
+      continue;
     }
+    if (ws_bytes < need || !ws) return FN2_E_WORKSPACE;
+    p.in_scale = in_scale;
+    for (int s = 0; s < ns; ++s) {
+      p.out[s] = outs ? outs[s0 + s] : nullptr;
+      p.pred[s] = preds ? preds[s0 + s] : nullptr;
+      p.dir[s] = dirs ? dirs[s0 + s] : nullptr;
+    }
+    p.epe = preds ? epe_sums + s0 : nullptr;
+    const int rc = C == 2 ? ms_launch<2>(p, smem, in, ws, st) : ms_launch<1>(p, smem, in, ws, st);
     if (rc != FN2_OK) return rc;
   }
   return FN2_OK;

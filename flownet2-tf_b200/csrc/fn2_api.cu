@@ -113,7 +113,8 @@ const char* fn2_error_string(int status) {
     case FN2_E_CUDA: return "CUDA error; see fn2_last_cuda_error";
     case FN2_E_NO_DEVICE: return "no sm_100 CUDA device is current";
     case FN2_E_UNSUPPORTED_GEOMETRY:
-      return "row halos need kernel_size 1, stride_1 1, pad == max_displacement and halo_top % stride_2 == 0";
+      return "unsupported geometry (row halos need kernel_size 1, stride_1 1, pad == max_displacement and "
+             "halo_top % stride_2 == 0; the fused loss needs C <= 2, in_w * C % 4 == 0 and reductions by >= 1.5)";
     default: return "unknown fn2 status";
   }
 }
@@ -275,16 +276,48 @@ int fn2_downsample_forward(const float* in, float* out, int N, int iH, int iW, i
   return downsample_forward(in, out, N, iH, iW, C, oH, oW, static_cast<cudaStream_t>(stream));
 }
 
-int fn2_downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
-                                 int iW, int C, void* stream) {
+static int check_scales(const int* out_hw, int num_scales, int N, int iH, int iW, int C) {
   if (N < 1 || iH < 1 || iW < 1 || C < 1 || num_scales < 1) return FN2_E_BAD_SHAPE;
-  if (!in || !outs || !out_hw || !aligned16(in)) return FN2_E_BAD_POINTER;
+  if (!out_hw) return FN2_E_BAD_POINTER;
   for (int s = 0; s < num_scales; ++s) {
     if (out_hw[2 * s] < 1 || out_hw[2 * s + 1] < 1) return FN2_E_BAD_SHAPE;
     if (out_hw[2 * s] < 2 || out_hw[2 * s + 1] < 2) return FN2_E_DOWNSAMPLE_SIZE;
-    if (!outs[s] || !aligned16(outs[s])) return FN2_E_BAD_POINTER;
   }
-  return downsample_multi_forward(in, outs, out_hw, num_scales, N, iH, iW, C, static_cast<cudaStream_t>(stream));
+  return FN2_OK;
+}
+
+size_t fn2_downsample_multi_workspace_bytes(const int* out_hw, int num_scales, int N, int iH, int iW, int C) {
+  if (check_scales(out_hw, num_scales, N, iH, iW, C) != FN2_OK) return 0;
+  return multiscale_workspace_bytes(out_hw, num_scales, N, iH, iW, C);
+}
+
+int fn2_downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
+                                 int iW, int C, void* ws, size_t ws_bytes, void* stream) {
+  const int rc = check_scales(out_hw, num_scales, N, iH, iW, C);
+  if (rc != FN2_OK) return rc;
+  if (!in || !outs || !aligned16(in)) return FN2_E_BAD_POINTER;
+  for (int s = 0; s < num_scales; ++s)
+    if (!outs[s] || !aligned16(outs[s])) return FN2_E_BAD_POINTER;
+  if (ws_bytes && (!ws || !aligned16(ws))) return FN2_E_BAD_POINTER;
+  return multiscale_forward(in, 1.0f, outs, nullptr, nullptr, nullptr, out_hw, num_scales, N, iH, iW, C, ws, ws_bytes,
+                            static_cast<cudaStream_t>(stream));
+}
+
+int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float* const* preds, const int* out_hw,
+                               int num_scales, int N, int iH, int iW, int C, float* const* downsampled,
+                               float* const* residual_dir, float* epe_sums, void* ws, size_t ws_bytes, void* stream) {
+  const int rc = check_scales(out_hw, num_scales, N, iH, iW, C);
+  if (rc != FN2_OK) return rc;
+  if (!(flow_scale == flow_scale)) return FN2_E_BAD_PARAM;
+  if (!flow || !preds || !epe_sums || !aligned16(flow)) return FN2_E_BAD_POINTER;
+  for (int s = 0; s < num_scales; ++s) {
+    if (!preds[s] || !aligned16(preds[s])) return FN2_E_BAD_POINTER;
+    if (downsampled && downsampled[s] && !aligned16(downsampled[s])) return FN2_E_BAD_POINTER;
+    if (residual_dir && residual_dir[s] && !aligned16(residual_dir[s])) return FN2_E_BAD_POINTER;
+  }
+  if (ws_bytes && (!ws || !aligned16(ws))) return FN2_E_BAD_POINTER;
+  return multiscale_forward(flow, flow_scale, downsampled, preds, residual_dir, epe_sums, out_hw, num_scales, N, iH, iW,
+                            C, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -94,9 +94,12 @@ int flow_warp_tile_forward_error(const float* image, const float* flow, const fl
 int flow_warp_forward_error(const float* image, const float* flow, const float* reference, float* out, float* err, int N,
                             int H, int W, int C, cudaStream_t st);
 int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C, int oH, int oW, cudaStream_t st);
-// downsample_multi.cu: several output sizes of one input in a single pass (host arrays of pointers / sizes)
-int downsample_multi_forward(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
-                             int iW, int C, cudaStream_t st);
+// downsample_multi.cu: several output sizes of one input in a single pass (host arrays of pointers / sizes), and the
+// end-point-error terms of the multi-scale loss against `preds` when given (dirs, epe_sums: see fn2ops.h)
+size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int iH, int iW, int C);
+int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
+                       float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
+                       int C, void* ws, size_t ws_bytes, cudaStream_t st);
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // floor / ceil division for possibly negative numerators (b > 0)

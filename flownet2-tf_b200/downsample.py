@@ -44,6 +44,27 @@ def downsample(tensor, size):
     return _forward(tensor, size)
 
 
+def _check_sizes(sizes):
+    sizes = [list(s) for s in sizes]
+    for s in sizes:
+        if len(s) != 2:  # downsample_kernel.cc:19
+            raise ValueError("size must be 2 dimensions")
+        if int(s[0]) < 1 or int(s[1]) < 1:
+            raise ValueError("Downsample: output dimensions must be positive")
+    return [(int(s[0]), int(s[1])) for s in sizes]
+
+
+def _multi_workspace(tensor, hw, nscales):
+    """Scratch for the fused multi-scale kernels (weight tables + per-tile partial sums); the library allocates nothing."""
+    import ctypes
+    N, H, W, C = tensor.shape
+    nbytes = _lib.lib().fn2_downsample_multi_workspace_bytes(hw, nscales, N, H, W, C)
+    if nbytes == 0:
+        return None, 0, ctypes.c_void_p(0)
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=tensor.device)
+    return ws, nbytes, ctypes.c_void_p(ws.data_ptr())
+
+
 def downsample_multi(tensor, sizes):
     """[downsample(tensor, size) for size in sizes] in one pass over ``tensor``.
 
@@ -54,20 +75,83 @@ def downsample_multi(tensor, sizes):
     _lib.require_cuda_f32(tensor, "input")
     if isinstance(tensor, torch.Tensor) and tensor.requires_grad:
         raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
-    sizes = [list(s) for s in sizes]
+    sizes = _check_sizes(sizes)
     if not sizes:
         return []
-    for s in sizes:
-        if len(s) != 2:  # downsample_kernel.cc:19
-            raise ValueError("size must be 2 dimensions")
-        if int(s[0]) < 1 or int(s[1]) < 1:
-            raise ValueError("Downsample: output dimensions must be positive")
     N, H, W, C = tensor.shape
-    outs = [torch.empty((N, int(s[0]), int(s[1]), C), dtype=torch.float32, device=tensor.device) for s in sizes]
+    outs = [torch.empty((N, h, w, C), dtype=torch.float32, device=tensor.device) for h, w in sizes]
     ptrs = (ctypes.c_void_p * len(outs))(*[o.data_ptr() for o in outs])
-    hw = (ctypes.c_int * (2 * len(outs)))(*[int(v) for s in sizes for v in s])
+    hw = (ctypes.c_int * (2 * len(outs)))(*[v for s in sizes for v in s])
     with torch.cuda.device(tensor.device):
-        st = _lib.lib().fn2_downsample_multi_forward(tensor.data_ptr(), ptrs, hw, len(outs), N, H, W, C,
+        ws, nbytes, wsp = _multi_workspace(tensor, hw, len(outs))
+        st = _lib.lib().fn2_downsample_multi_forward(tensor.data_ptr(), ptrs, hw, len(outs), N, H, W, C, wsp, nbytes,
                                                      _lib.current_stream_ptr(tensor.device))
     _lib.check(st, "Downsample")
     return outs
+
+
+class _MultiscaleEpe(torch.autograd.Function):
+    """epe[s] = average_endpoint_error(downsample(flow * scale, size_s), predictions[s]) for every s, one pass.
+
+    Differentiable with respect to the predictions (the kernel also writes (pred - down) / epe, which is all the
+    gradient needs); the ground-truth flow gets none, as in the reference (downsample has no registered gradient)."""
+
+    @staticmethod
+    def forward(ctx, flow, scale, want_down, *preds):
+        import ctypes
+        N, H, W, C = flow.shape
+        sizes = [(int(p.shape[1]), int(p.shape[2])) for p in preds]
+        k = len(preds)
+        need_grad = any(ctx.needs_input_grad[3:])
+        dirs = [torch.empty_like(p) for p in preds] if need_grad else []
+        downs = [torch.empty_like(p) for p in preds] if want_down else []
+        epe = torch.empty(k, dtype=torch.float32, device=flow.device)
+        arr = ctypes.c_void_p * k
+        pp = arr(*[p.data_ptr() for p in preds])
+        dp = arr(*[d.data_ptr() for d in dirs]) if dirs else None
+        op = arr(*[d.data_ptr() for d in downs]) if downs else None
+        hw = (ctypes.c_int * (2 * k))(*[v for s in sizes for v in s])
+        with torch.cuda.device(flow.device):
+            ws, nbytes, wsp = _multi_workspace(flow, hw, k)
+            st = _lib.lib().fn2_multiscale_epe_forward(flow.data_ptr(), float(scale), pp, hw, k, N, H, W, C, op, dp,
+                                                       epe.data_ptr(), wsp, nbytes,
+                                                       _lib.current_stream_ptr(flow.device))
+        _lib.check(st, "MultiscaleEpe")
+        ctx.save_for_backward(*dirs)
+        ctx.n, ctx.k = N, k
+        ctx.mark_non_differentiable(*downs)
+        return (epe,) + tuple(downs)
+
+    @staticmethod
+    def backward(ctx, g_epe, *unused):
+        dirs = ctx.saved_tensors
+        if not dirs:
+            return (None,) * (3 + ctx.k)
+        grads = tuple((g_epe[s] / ctx.n) * d if ctx.needs_input_grad[3 + s] else None for s, d in enumerate(dirs))
+        return (None, None, None) + grads
+
+
+def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
+    """Per-scale data terms of the FlowNet training loss in ONE pass over ``flow``.
+
+    For predictions p_s of shape [N,h_s,w_s,C] returns the tensor
+        epe[s] = sum_pixels sqrt(sum_c (p_s - downsample(flow * flow_scale, [h_s, w_s]))^2) / N
+    i.e. ``average_endpoint_error(downsample(flow * 0.05, size), predict_flow)`` of ``flownet_c.py:127-160`` /
+    ``utils.py:209-224`` for all scales, without materialising the scaled flow or re-reading it per scale, and with the
+    reductions done by the kernel in a fixed order.  Differentiable w.r.t. the predictions.  With
+    ``return_downsampled=True`` also returns the list of downsampled tensors."""
+    _lib.require_cuda_f32(flow, "flow")
+    if flow.requires_grad:
+        raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
+    predictions = list(predictions)
+    if not predictions:
+        raise ValueError("at least one prediction is needed")
+    N, H, W, C = flow.shape
+    for p in predictions:
+        _lib.require_cuda_f32(p, "prediction")
+        if p.shape[0] != N or p.shape[3] != C:
+            raise ValueError("prediction %s does not match flow %s" % (tuple(p.shape), tuple(flow.shape)))
+        if p.device != flow.device:
+            raise ValueError("predictions and flow must be on the same device")
+    res = _MultiscaleEpe.apply(flow, float(flow_scale), bool(return_downsampled), *predictions)
+    return (res[0], list(res[1:])) if return_downsampled else res[0]

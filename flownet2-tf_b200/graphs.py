@@ -32,7 +32,8 @@ def default_ops(precision=None):
     """This package's CUDA ops behind the reference's three signatures (+ the fused multi-scale downsample)."""
     from .correlation import correlation as _correlation, correlation_leaky_concat as _fused
     from .flow_warp import flow_warp as _flow_warp, flow_warp_error as _flow_warp_error
-    from .downsample import downsample as _downsample, downsample_multi as _downsample_multi
+    from .downsample import downsample as _downsample, downsample_multi as _downsample_multi, \
+        multiscale_epe as _multiscale_epe
 
     def corr(a, b, k, md, s1, s2, pad):
         return _correlation(a, b, k, md, s1, s2, pad, precision=precision)
@@ -40,7 +41,8 @@ def default_ops(precision=None):
     def corr_fused(a, b, k, md, s1, s2, pad, buf, offset, slope):
         return _fused(a, b, k, md, s1, s2, pad, buf, offset, slope, precision=precision)
     return SimpleNamespace(correlation=corr, flow_warp=_flow_warp, downsample=_downsample,
-                           downsample_multi=_downsample_multi, correlation_leaky_concat=corr_fused,
+                           downsample_multi=_downsample_multi, multiscale_epe=_multiscale_epe,
+                           correlation_leaky_concat=corr_fused,
                            flow_warp_error=_flow_warp_error)
 
 
@@ -401,8 +403,13 @@ def multiscale_loss(flow, predictions, ops, gt_scale=0.05, weights=LOSS_WEIGHTS)
     (gt_scale 20.0: flownet_sd.py:121-160): the ground-truth flow, scaled, is downsampled to the size of each of
     predict_flow6..2 and compared by average end-point error; weights 0.32, 0.08, 0.02, 0.01, 0.005.  The five
     downsample() calls of the reference are one fused pass here (``ops.downsample_multi``) when the ops offer it."""
-    flow = (flow * gt_scale).contiguous()
     preds = [predictions["predict_flow%d" % k] for k in (6, 5, 4, 3, 2)]
+    if hasattr(ops, "multiscale_epe"):
+        # one fused pass: flow * gt_scale on load, the five downsamples, the five end-point-error sums (f-3)
+        epe = ops.multiscale_epe(flow.contiguous(), [p.contiguous() for p in preds], gt_scale)
+        losses = [epe[i] for i in range(len(preds))]
+        return weighted_loss(losses, weights), losses
+    flow = (flow * gt_scale).contiguous()
     sizes = [(int(p.shape[1]), int(p.shape[2])) for p in preds]
     if hasattr(ops, "downsample_multi"):
         downs = ops.downsample_multi(flow, sizes)

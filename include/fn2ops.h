@@ -47,7 +47,8 @@ typedef enum fn2_status {
   FN2_E_CUDA = -10,            /* a CUDA runtime/driver call failed; see fn2_last_cuda_error()          */
   FN2_E_NO_DEVICE = -11,       /* no sm_100 device is current                                           */
   FN2_E_UNSUPPORTED_GEOMETRY = -12 /* *_halo entry points: need kernel_size 1, stride_1 1, pad == max_displacement,
-                                  halo_top a multiple of stride_2                                       */
+                                  halo_top a multiple of stride_2; fn2_multiscale_epe_forward: shapes the
+                                  fused multi-scale kernels do not take                                 */
 } fn2_status;
 
 /* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode.
@@ -177,9 +178,32 @@ FN2_API int fn2_downsample_forward(const float* input, float* output, int N, int
  * edge maps likewise in the HFEM losses, utils.py:227-339): outputs[s] = downsample(input, [out_hw[2s], out_hw[2s+1]])
  * for s < num_scales, every scale computed directly from `input` with the arithmetic of fn2_downsample_forward, the
  * input read from HBM once.  `outputs` (num_scales device pointers) and `out_hw` (2*num_scales ints) are HOST arrays,
- * consumed before the call returns. */
+ * consumed before the call returns.  `workspace`: fn2_downsample_multi_workspace_bytes() bytes of device memory. */
 FN2_API int fn2_downsample_multi_forward(const float* input, float* const* outputs, const int* out_hw, int num_scales,
-                                 int N, int in_h, int in_w, int C, void* stream);
+                                 int N, int in_h, int in_w, int C, void* workspace, size_t workspace_bytes,
+                                 void* stream);
+
+/* Scratch bytes of the two multi-scale entry points (tables that depend on the shapes only, and the per-tile partial
+ * sums of the band pass).  0 when every scale goes through the single-scale kernels (C > 2, upsampling, odd widths). */
+FN2_API size_t fn2_downsample_multi_workspace_bytes(const int* out_hw, int num_scales, int N, int in_h, int in_w, int C);
+
+/* The data term of the multi-scale training loss in the same pass (second half).  Replaces,
+ * for every scale s, the graph nodes of flownet_c.py:127-160 + utils.py:209-224:
+ *     flow_s   = downsample(flow * flow_scale, [out_hw[2s], out_hw[2s+1]])          (flow * 0.05: flownet_c.py:128)
+ *     epe_s    = sqrt(reduce_sum(square(predictions[s] - flow_s), axis=3))
+ *     epe_sums[s] = reduce_sum(epe_s) / N                                             (average_endpoint_error)
+ * flow [N,in_h,in_w,C] is multiplied by flow_scale on load (a rounded fp32 product, exactly the materialised tensor of
+ * the reference); predictions[s] is [N,out_h,out_w,C].  Optional outputs (the array, or single entries, may be NULL):
+ * downsampled[s] = flow_s, residual_dir[s] = (predictions[s] - flow_s) / epe_s, the factor the gradient of epe_sums[s]
+ * with respect to predictions[s] is made of (0/0 = NaN where the error is exactly 0, as the gradient of sqrt there).
+ * epe_sums is a DEVICE array of num_scales floats; the sums are formed in a fixed order (bit-reproducible).
+ * `predictions`, `downsampled`, `residual_dir` and `out_hw` are HOST arrays consumed before the call returns.
+ * Needs the fused kernels (C <= 2, in_w * C a multiple of 4, every scale a reduction by >= 1.5):
+ * FN2_E_UNSUPPORTED_GEOMETRY otherwise. */
+FN2_API int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float* const* predictions,
+                               const int* out_hw, int num_scales, int N, int in_h, int in_w, int C,
+                               float* const* downsampled, float* const* residual_dir, float* epe_sums,
+                               void* workspace, size_t workspace_bytes, void* stream);
 
 /* Number of kernel launches (library kernels, not memsets) enqueued by this process so far; bench.py reports the
  * difference over its timed region as `gpu_launches`. */

@@ -86,3 +86,6 @@ if want("warp") or want("down"):
         sizes = [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]
         timed("downsample_multi", lambda i: fn2.downsample_multi(FLO[i], sizes),
               flo + sum(N * h * w * 2 * f for h, w in sizes))
+        PR = [rnd(N, h, w, 2) for h, w in sizes]
+        timed("multiscale_epe", lambda i: fn2.multiscale_epe(FLO[i], PR, 0.05),
+              flo + sum(N * h * w * 2 * f for h, w in sizes))
