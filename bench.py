@@ -7,12 +7,18 @@ One *step* = one pass of the hot path over one batch of B synthetic 512x384 imag
     downsample of the ground-truth flow [B,384,512,2] to the five loss scales (flownet_c.py:135-160)
 metric = image pairs / s (whole job, all GPUs; batch-sharded, no collective on the data path => weak scaling).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp32|tf32|bf16|tf32x3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision auto|fp32|tf32x3|tf32]
+                    [--config hotpath|strips4k]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
-Prints ONE JSON line on rank 0.  `--impl reference` times the CPU restatement of the reference ops (the reference
-has no CPU implementation of these ops and its TF GPU ops cannot be built here) on all host threads.
+Prints ONE JSON line on rank 0.  The headline runs the correlation at the drop-in default precision ("auto" =
+split-tf32, which meets the reference's float32 tolerance); `per_precision` carries the other modes.  Extra keys:
+`cfg1` (one pair, warm and cold L2), `cfg2` (batch-8 warp + downsample), `reference_gpu_kernels` (the reference's own
+CUDA kernels on this GPU, per op), `e2e_copy_ceiling`, and with N > 1 `strips4k` (BASELINE config 5: the 4K
+correlation cut into row strips, NCCL halo exchange inside the timed region; also `--config strips4k` on its own).
+`--impl reference` times the CPU restatement of the reference ops (the reference has no CPU implementation of these
+ops and its TF GPU ops cannot be built here) on all host threads.
 """
 import argparse
 import json
@@ -29,6 +35,8 @@ DS_SIZES = [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]
 CORR_ARGS = (1, 20, 1, 2, 20)
 HC, WC, CC, D = 48, 64, 256, 441
 HI, WI = 384, 512
+H4K, W4K = 272, 480          # conv3 of a 3840x2160 pair padded to 3840x2176 (net.py:301-309)
+REF_SAMPLE = 16              # pairs per step of the CPU arm
 
 
 def parse():
@@ -38,19 +46,21 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("FN2_BENCH_PRECISION", "auto"))
+    ap.add_argument("--config", default="hotpath", choices=["hotpath", "strips4k"])
     ap.add_argument("--eager", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--batch", type=int, default=32, help="image pairs per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip per_precision / cfg1 / cfg2 / strips4k extras")
     return ap.parse_args()
 
 
 # ---------------------------------------------------------------------------------------------- bytes per pair
-def algorithmic_bytes(batch):
+def algorithmic_bytes(batch, hc=HC, wc=WC):
     """Algorithmic HBM bytes per launch group, SURVEY.md section 8(d): every tensor read or written once."""
     f = 4
-    act, vol = HC * WC * CC * f, HC * WC * D * f
+    act, vol = hc * wc * CC * f, hc * wc * D * f
     img, flo = HI * WI * 3 * f, HI * WI * 2 * f
     ds_out = sum(h * w * 2 * f for h, w in DS_SIZES)
     return {
@@ -62,8 +72,35 @@ def algorithmic_bytes(batch):
     }
 
 
-def corr_flops(batch):
-    return {"corr_fwd": batch * 2.0 * HC * WC * D * CC, "corr_bwd": batch * 4.0 * HC * WC * D * CC}
+def corr_flops(batch, hc=HC, wc=WC):
+    return {"corr_fwd": batch * 2.0 * hc * wc * D * CC, "corr_bwd": batch * 4.0 * hc * wc * D * CC}
+
+
+def executed_mma_flops(batch, precision, hc=HC, wc=WC):
+    """FLOPs the tensor-core kernels actually issue (band tiles include pairs outside the +-10 window), from their
+    tilings: corr_tc.cu (8-row pair tiles, 4 b-rows x 32 cols per block, M256 N128), corr_tc_x3.cu (2-row tiles,
+    M128 N256 with the hi/lo split folded in), corr_tc_bwd.cu (8-row tiles, one item per source row, M128 N256 K32 per
+    128 channels; three MMAs per step in the split mode).  Parity classes: (hc/2) x (wc/2) pixels each."""
+    if precision not in ("tf32", "tf32x3"):
+        return None
+    hcl, wcl = (hc + 1) // 2, (wc + 1) // 2
+    tx = (wcl + 31) // 32
+    nhx = 2 if tx > 1 else 1
+    rows_f = 8 if (precision == "tf32" and tx == 1) else (4 if precision == "tf32" else 2)
+    fwd = 0.0
+    for y0 in range(0, hcl, rows_f):
+        lo, hi = max(0, y0 - 10), min(hcl - 1, y0 + rows_f - 1 + 10)
+        blocks = (hi - lo + 1 + 3) // 4 * nhx
+        m = {8: 256, 4: 128, 2: 128}[rows_f]
+        n = 256 if precision == "tf32x3" else 128
+        fwd += blocks * 2.0 * m * n * CC
+    bwd = 0.0
+    for r0 in range(0, hcl, 8):
+        lo, hi = max(0, r0 - 10), min(hcl - 1, r0 + 7 + 10)
+        items = (hi - lo + 1) * nhx
+        bwd += items * 2.0 * CC * 256 * 32 * (3 if precision == "tf32x3" else 1)
+    per_image = 4 * tx
+    return {"corr_fwd": batch * per_image * fwd, "corr_bwd": batch * per_image * bwd * 2}
 
 
 # ------------------------------------------------------------------------------------------------- clocks
@@ -116,7 +153,6 @@ def cpu_pass(o, data, n):
 
 
 def host_data(batch, seed=0):
-    import numpy as np
     import torch
     gen = torch.Generator().manual_seed(1234 + seed)
     lr = torch.nn.functional.leaky_relu
@@ -136,7 +172,10 @@ def use_all_host_threads():
     """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host thread.  Returns the thread count
     OpenMP will actually use (the number reported as `cores`)."""
     import ctypes
-    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
     os.environ["OMP_NUM_THREADS"] = str(n)
     try:
         gomp = ctypes.CDLL("libgomp.so.1")
@@ -146,16 +185,26 @@ def use_all_host_threads():
         return n
 
 
+def workload_config(batch):
+    """The same dict in both arms (ours and --impl reference): the workload, not the implementation."""
+    return {"workload": "hot path over %d synthetic 512x384 pairs per GPU: correlation fwd+bwd @ FlowNetC conv3 "
+                        "[%d,48,64,256]->[%d,48,64,441] (k=1,d=20,s1=1,s2=2,pad=20) + flow_warp fwd+bwd "
+                        "[%d,384,512,3] + downsample of GT flow to 5 loss scales" % (batch, batch, batch, batch),
+            "pairs_per_gpu": batch, "parallelism": "batch-sharded replicas",
+            "l2": "inputs larger than L2 (1.6 GB per step vs 126 MB)"}
+
+
 def run_reference(args, rank):
-    """--impl reference: the CPU restatement of the reference ops on all host threads, bounded sample per step."""
+    """--impl reference: the CPU restatement of the reference ops on all host threads; every step is a bounded sample
+    (REF_SAMPLE pairs) of the batch, with the warm-up the caller asked for."""
     if rank != 0:
         return
     from oracle import oracle as o
     o.lib()
     cores = use_all_host_threads()
-    sample = 4
+    sample = min(REF_SAMPLE, args.batch)
     data = [x.numpy() for x in host_data(sample)]
-    for _ in range(min(args.warmup, 1)):
+    for _ in range(args.warmup):
         cpu_pass(o, data, sample)
     t0 = time.time()
     for _ in range(args.steps):
@@ -164,9 +213,9 @@ def run_reference(args, rank):
     val = sample * args.steps / dt
     line = {
         "impl": "reference", "metric": "image_pairs_per_s", "value": val, "unit": "pairs/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.batch, "fp32"),
+        "config": workload_config(args.batch),
         "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": cores, "kind": "port",
                          "sample": "%d pairs per step (of the %d-pair batch), C restatement oracle/fn2_oracle.c, "
                                    "OpenMP on %d threads" % (sample, args.batch, cores)},
@@ -176,13 +225,148 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(batch, precision):
-    return {"workload": "hot path over %d synthetic 512x384 pairs per GPU: correlation fwd+bwd @ FlowNetC conv3 "
-                        "[%d,48,64,256]->[%d,48,64,441] (k=1,d=20,s1=1,s2=2,pad=20) + flow_warp fwd+bwd "
-                        "[%d,384,512,3] + downsample of GT flow to 5 loss scales" % (batch, batch, batch, batch),
-            "pairs_per_gpu": batch, "correlation_precision": precision, "parallelism": "batch-sharded replicas",
-            "l2": "inputs larger than L2 (1.6 GB per step vs 126 MB)",
-            "launch": "CUDA graph replay per op, 5 per step (eager launches with --eager)"}
+# --------------------------------------------------------------------------------------------- timing helpers
+def graph_time(torch, fns, reps, stream, rounds=3):
+    """Median device time (ms) of ONE pass over the list of callables `fns`, each a (rotating) variant of the same op:
+    they are captured into one CUDA graph so that consecutive launches never find their inputs in L2, and the graph
+    replay is timed with CUDA events on `stream`."""
+    with torch.cuda.stream(stream):
+        for fn in fns:
+            fn()
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=stream):
+            keep = [fn() for fn in fns]
+        for _ in range(2):
+            gr.replay()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(rounds):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(reps):
+                gr.replay()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) / (reps * len(fns)))
+    del keep
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def op_entry(ms, nbytes, hbm_peak, flops=None, mma=None, tf32_peak=None):
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    e = {"ms": round(ms, 4), "algorithmic_mb": round(nbytes / 1e6, 2), "gb_s": round(gbs, 1),
+         "hbm_frac": round(gbs / hbm_peak, 4)}
+    if flops:
+        e["useful_tflop_s"] = round(flops / (ms * 1e-3) / 1e12, 2)
+    if mma and tf32_peak:
+        e["mma_tflop_s"] = round(mma / (ms * 1e-3) / 1e12, 1)
+        e["tensor_frac"] = round(mma / (ms * 1e-3) / 1e12 / tf32_peak, 4)
+    return e
+
+
+def load_peaks():
+    peaks, src = {}, "fallback"
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        src = "measured"
+    except Exception:
+        pass
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    # kind::tf32 runs at half the bf16 rate (K = 8 against 16 per instruction); no tf32 GEMM is measured by the driver
+    tf32 = float(peaks.get("bf16_tflops", 1590.0)) / 2.0
+    return hbm, tf32, src
+
+
+# ----------------------------------------------------------------------------------------- strips (config 5)
+def strips_bench(torch, dist, fn2, dev, rank, world, precision, steps, warm, hbm_peak):
+    """BASELINE config 5: ONE 4K pair's conv3 correlation [1,272,480,256], forward + backward, cut into `world` row
+    strips (strong scaling); the halo rows of input_b and the mirror halo of backprops_b travel by NCCL send/recv inside
+    the timed region, overlapped with the interior rows (flownet2_tf_b200.strips)."""
+    from flownet2_tf_b200 import strips
+    if H4K % world != 0 or (H4K // world) % 2 != 0 or H4K // world < 20:
+        return {"unavailable": "272 rows do not split into %d even strips of >= 20 rows" % world}
+    rows = H4K // world
+    gen = torch.Generator(device=dev).manual_seed(77 + rank)
+    lr = torch.nn.functional.leaky_relu
+    a = lr(torch.randn(1, rows, W4K, CC, device=dev, generator=gen), 0.1).requires_grad_()
+    if world > 1:
+        b_ext, b_view = strips.alloc_b_ext(1, rows, W4K, CC, dev)
+        b_view.copy_(lr(torch.randn(1, rows, W4K, CC, device=dev, generator=gen), 0.1))
+        b = b_view.detach().requires_grad_()
+    else:
+        b_ext = None
+        b = lr(torch.randn(1, rows, W4K, CC, device=dev, generator=gen), 0.1).requires_grad_()
+    go = torch.randn(1, rows, W4K, D, device=dev, generator=gen)
+
+    def step():
+        a.grad = None
+        b.grad = None
+        if world > 1:
+            out = strips.correlation_strips(a, b, *CORR_ARGS, precision=precision, b_ext=b_ext)
+        else:
+            out = fn2.correlation(a, b, *CORR_ARGS, precision=precision)
+        out.backward(go)
+        return out
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(warm, 3)):
+        step()
+    sync()
+    # the exchange alone (what the limiting collective costs): 20 rows of b each way per boundary, ncclSend/Recv
+    comm_ms = None
+    if world > 1:
+        h = strips.halo_rows(CORR_ARGS[1], CORR_ARGS[3])
+        up, down = strips._neighbours(None)
+        own = b_ext[:, (h if up is not None else 0):][:, :rows]
+        su, sd = own[:, :h], own[:, rows - h:]
+        ru = torch.empty_like(su) if up is not None else None
+        rd = torch.empty_like(sd) if down is not None else None
+        for _ in range(3):
+            strips._finish(strips._start_exchange(su, ru, sd, rd, up, down, None))
+        sync()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            strips._finish(strips._start_exchange(su, ru, sd, rd, up, down, None))
+        e1.record()
+        sync()
+        t = torch.tensor([e0.elapsed_time(e1) / 20], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        comm_ms = float(t.item())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ab, fl = algorithmic_bytes(1, H4K, W4K), corr_flops(1, H4K, W4K)
+    nbytes = ab["corr_fwd"] + ab["corr_bwd"]
+    return {
+        "workload": "one 4K pair: correlation fwd+bwd at conv3 [1,272,480,256]->[1,272,480,441], %d row strips of %d"
+                    % (world, rows),
+        "precision": precision, "scaling": "strong", "n_gpus": world, "steps": steps, "ms_per_step": round(ms, 4),
+        "pairs_per_s": round(1e3 / ms, 1), "gb_s_aggregate": round(nbytes / (ms * 1e-3) / 1e9, 1),
+        "hbm_frac_of_n_gpus": round(nbytes / (ms * 1e-3) / 1e9 / (hbm_peak * world), 4),
+        "useful_tflop_s": round((fl["corr_fwd"] + fl["corr_bwd"]) / (ms * 1e-3) / 1e12, 1),
+        "collective": None if world == 1 else {
+            "what": "ncclSend/ncclRecv (torch.distributed batch_isend_irecv), 20 rows of input_b per direction per "
+                    "boundary in forward, 20 rows of backprops_b partial sums in backward",
+            "bytes_per_direction_per_boundary": 20 * W4K * CC * 4, "comm_nranks": world,
+            "exchange_alone_ms": round(comm_ms, 4), "overlapped_with": "interior rows of the strip"},
+        "launch": "eager autograd calls (correlation_strips forward + backward)",
+    }
 
 
 # ------------------------------------------------------------------------------------------------------ ours
@@ -194,6 +378,19 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+
+    # With several ranks on one host, give each its own slice of the cores (its pinned buffers are then first-touched
+    # and its copy threads run next to each other instead of all ranks sharing every core).
+    affinity = None
+    if world > 1 and hasattr(os, "sched_getaffinity"):
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = len(cores) // world
+            if per >= 1:
+                os.sched_setaffinity(0, cores[local * per:(local + 1) * per])
+                affinity = "%d cores per rank (%d-%d for rank 0)" % (per, cores[0], cores[per - 1])
+        except OSError:
+            pass
 
     import torch
     import torch.distributed as dist
@@ -208,37 +405,53 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()
+    hbm_peak, tf32_peak, peak_src = load_peaks()
 
     precision = args.precision
     if precision == "auto":
-        # the tcgen05 path is the one BASELINE.json's target is stated for; its tolerance is in tests/test_gpu_tc.py
-        precision = "tf32"
+        precision = "tf32x3"   # what fn2.correlation() runs by default for this call: meets the fp32 tolerance
     B = args.batch
-    host = host_data(B, seed=rank)
-    a, b, g, image, flow, gimg, gt = [x.to(dev) for x in host]
-    ops = ["corr_fwd", "corr_bwd", "warp_fwd", "warp_bwd", "downsample"]
-
-    def step(ev=None):
-        def mark(i):
-            if ev is not None:
-                ev[i].record()
-        mark(0)
-        out = fn2.correlation(a, b, *CORR_ARGS, precision=precision)
-        mark(1)
-        ga, gb = fn2.correlation_grad(g, a, b, *CORR_ARGS, precision=precision)
-        mark(2)
-        warped = fn2.flow_warp(image, flow)
-        mark(3)
-        gi, gf = fn2.flow_warp_grad(image, flow, gimg)
-        mark(4)
-        ds = fn2.downsample_multi(gt, DS_SIZES)
-        mark(5)
-        return out, ga, gb, warped, gi, gf, ds
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.config == "strips4k":
+        res = strips_bench(torch, dist, fn2, dev, rank, world, precision, args.steps, args.warmup, hbm_peak)
+        if rank == 0:
+            line = {"metric": "image_pairs_per_s", "value": res.get("pairs_per_s"), "unit": "pairs/s (4K pairs)",
+                    "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                    "ms_per_step": res.get("ms_per_step"), "higher_is_better": True, "scaling": "strong",
+                    "vs_baseline": None, "dtype": precision, "data": "synthetic",
+                    "config": {"workload": res.get("workload"), "parallelism": "row strips + NCCL halo exchange"},
+                    "strips4k": res}
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    host = host_data(B, seed=rank)
+    a, b, g, image, flow, gimg, gt = [x.to(dev) for x in host]
+    ops = ["corr_fwd", "corr_bwd", "warp_fwd", "warp_bwd", "downsample"]
+
+    op_fns = [
+        lambda: fn2.correlation(a, b, *CORR_ARGS, precision=precision),
+        lambda: fn2.correlation_grad(g, a, b, *CORR_ARGS, precision=precision),
+        lambda: fn2.flow_warp(image, flow),
+        lambda: fn2.flow_warp_grad(image, flow, gimg),
+        lambda: fn2.downsample_multi(gt, DS_SIZES),
+    ]
+
+    def step(ev=None):
+        res = []
+        for i, fn in enumerate(op_fns):
+            if ev is not None:
+                ev[i].record()
+            res.append(fn())
+        if ev is not None:
+            ev[5].record()
+        return res
 
     warm = max(args.warmup, 3)
     for _ in range(warm):
@@ -249,13 +462,6 @@ def main():
     # stream); a step = five graph replays with an event between them, so the per-op device times come from INSIDE
     # the timed region and the region is free of Python launch latency.  --eager times plain launches instead.
     side = torch.cuda.Stream(device=dev)
-    op_fns = [
-        lambda: fn2.correlation(a, b, *CORR_ARGS, precision=precision),
-        lambda: fn2.correlation_grad(g, a, b, *CORR_ARGS, precision=precision),
-        lambda: fn2.flow_warp(image, flow),
-        lambda: fn2.flow_warp_grad(image, flow, gimg),
-        lambda: fn2.downsample_multi(gt, DS_SIZES),
-    ]
     graphs, keep, launches_per_step = [], [], 0
     if not args.eager:
         with torch.cuda.stream(side):
@@ -291,8 +497,7 @@ def main():
     barrier()
     t1 = time.time()
     launches = launches_per_step * args.steps if graphs else _lib.launch_count() - launches0
-    last = 5
-    elapsed_ms = evs[0][0].elapsed_time(evs[args.steps - 1][last])
+    elapsed_ms = evs[0][0].elapsed_time(evs[args.steps - 1][5])
     clocks = sampler.stop(t0, t1) if sampler else None
     if world > 1:
         t = torch.tensor([elapsed_ms], device=dev)
@@ -310,7 +515,8 @@ def main():
     # Every step uploads ALL of its inputs from pinned host memory and downloads ALL of its results.  Three streams
     # (upload / compute / download) with double-buffered device inputs and host outputs let step k+1's upload run
     # under step k's compute and download (PCIe is full duplex); nothing is skipped or reused between steps.
-    e2e = None
+    # `e2e_copy_ceiling` is the same loop with the compute left out: what the box's host memory / PCIe path allows.
+    e2e = ceiling = None
     if not args.no_e2e:
         pinned = [x.pin_memory() for x in host]
         h2d = sum(x.numel() * 4 for x in pinned)
@@ -324,7 +530,7 @@ def main():
         dn_done = [torch.cuda.Event() for _ in range(2)]
         live = [None, None]
 
-        def e2e_step(k):
+        def e2e_step(k, compute=True):
             sl = k & 1
             with torch.cuda.stream(s_up):
                 s_up.wait_event(cp_done[sl])          # step k-2 has finished reading this input set
@@ -333,14 +539,17 @@ def main():
                 up_done[sl].record(s_up)
             s_cp.wait_event(up_done[sl])
             s_cp.wait_event(dn_done[sl])              # step k-2's results have left the device
-            da, db, dg, dimg, dflow, dgimg, dgt = dev_in[sl]
-            res = [fn2.correlation(da, db, *CORR_ARGS, precision=precision)]
-            res += list(fn2.correlation_grad(dg, da, db, *CORR_ARGS, precision=precision))
-            res.append(fn2.flow_warp(dimg, dflow))
-            res += list(fn2.flow_warp_grad(dimg, dflow, dgimg))
-            res += fn2.downsample_multi(dgt, DS_SIZES)
+            if compute:
+                da, db, dg, dimg, dflow, dgimg, dgt = dev_in[sl]
+                res = [fn2.correlation(da, db, *CORR_ARGS, precision=precision)]
+                res += list(fn2.correlation_grad(dg, da, db, *CORR_ARGS, precision=precision))
+                res.append(fn2.flow_warp(dimg, dflow))
+                res += list(fn2.flow_warp_grad(dimg, dflow, dgimg))
+                res += fn2.downsample_multi(dgt, DS_SIZES)
+                live[sl] = res                        # keep the device results alive until their download ran
+            else:
+                res = live[sl]
             cp_done[sl].record(s_cp)
-            live[sl] = res                            # keep the device results alive until their download ran
             if host_out[sl] is None:
                 host_out[sl] = [torch.empty(r.shape, dtype=r.dtype).pin_memory() for r in res]
             with torch.cuda.stream(s_dn):
@@ -350,28 +559,48 @@ def main():
                     r.record_stream(s_dn)
                 dn_done[sl].record(s_dn)
 
+        def e2e_run(compute):
+            barrier()
+            s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s2.record(s_cp)
+            s_up.wait_event(s2)
+            for k in range(e2e_steps):
+                e2e_step(k, compute)
+            s_cp.wait_event(dn_done[0])
+            s_cp.wait_event(dn_done[1])
+            e2.record(s_cp)
+            barrier()
+            ms = s2.elapsed_time(e2)
+            if world > 1:
+                t = torch.tensor([ms], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            return ms
+
         for k in range(4):
             e2e_step(k)
-        barrier()
-        s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s2.record(s_cp)
-        s_up.wait_event(s2)
-        for k in range(e2e_steps):
-            e2e_step(k)
-        s_cp.wait_event(dn_done[0])
-        s_cp.wait_event(dn_done[1])
-        e2.record(s_cp)
-        barrier()
-        ms = s2.elapsed_time(e2)
-        if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        ms = e2e_run(True)
         d2h = sum(h.numel() * 4 for h in host_out[0])
         e2e = {"value": world * B * e2e_steps / (ms / 1e3), "unit": "pairs/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": ms / e2e_steps,
                "how": "public Python API, pinned host inputs and outputs, upload/compute/download streams"}
+        ms = e2e_run(False)
+        ceiling = {"value": world * B * e2e_steps / (ms / 1e3), "unit": "pairs/s", "ms_per_step": ms / e2e_steps,
+                   "gb_s_per_gpu_each_way": [round(h2d / (ms / e2e_steps * 1e-3) / 1e9, 1),
+                                             round(d2h / (ms / e2e_steps * 1e-3) / 1e9, 1)],
+                   "what": "the same loop with the compute left out: pinned H2D of every input and D2H of every result "
+                           "of a step on all %d ranks at once (one cudaMemcpyAsync per tensor); the part of the e2e "
+                           "loss that belongs to the box" % world,
+                   "cpu_affinity": affinity}
         del live, dev_in
+
+    # ---- config 5 inside the default multi-GPU run, so that the scaling run records a data-path collective ----
+    strips4k = None
+    if world > 1 and not args.no_extras:
+        try:
+            strips4k = strips_bench(torch, dist, fn2, dev, rank, world, precision, 20, 3, hbm_peak)
+        except Exception as exc:  # pragma: no cover
+            strips4k = {"unavailable": str(exc)[:300]}
 
     if rank != 0:
         if world > 1:
@@ -379,28 +608,18 @@ def main():
         return
 
     # ---- roofline of the dominant kernel ------------------------------------------------------------------
-    peaks, peak_src = {}, "fallback"
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        peak_src = "measured"
-    except Exception:
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     abytes, flops = algorithmic_bytes(B), corr_flops(B)
+    mma = executed_mma_flops(B, precision) or {}
     dominant = max(per_op_ms, key=per_op_ms.get)
-    per_op = {}
-    for name in ops:
-        gbs = abytes[name] / (per_op_ms[name] * 1e-3) / 1e9
-        per_op[name] = {"ms": round(per_op_ms[name], 4), "algorithmic_mb": round(abytes[name] / 1e6, 2),
-                        "gb_s": round(gbs, 1), "hbm_frac": round(gbs / hbm_peak, 4)}
-        if name in flops:
-            per_op[name]["useful_tflop_s"] = round(flops[name] / (per_op_ms[name] * 1e-3) / 1e12, 2)
+    per_op = {name: op_entry(per_op_ms[name], abytes[name], hbm_peak, flops.get(name), mma.get(name), tf32_peak)
+              for name in ops}
     achieved = per_op[dominant]["gb_s"]
     roofline = {"kernel": dominant, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": round(achieved / hbm_peak, 4), "traffic": None, "peak_source": peak_src,
                 "correlation_fwd_bwd_hbm_frac": round(
                     (abytes["corr_fwd"] + abytes["corr_bwd"]) / ((per_op_ms["corr_fwd"] + per_op_ms["corr_bwd"]) * 1e-3)
-                    / 1e9 / hbm_peak, 4)}
+                    / 1e9 / hbm_peak, 4),
+                "tf32_peak_tflops": tf32_peak, "tf32_peak_source": "bf16 peak (%s) / 2" % peak_src}
     # DRAM bytes per launch (read + write) from the committed `ncu --set full` captures of these kernels at batch 32
     # (profiles/traffic.json, written by tools/make_traffic.py); only valid for the batch it was captured at
     prof = os.path.join(ROOT, "profiles", "traffic.json")
@@ -414,13 +633,41 @@ def main():
         except Exception:
             pass
 
+    extras = world == 1 and not args.no_extras
+    tstream = torch.cuda.Stream(device=dev)
+
+    # ---- the correlation at every precision mode, same batch, same timing method ------------------------------
+    per_precision = None
+    if extras:
+        per_precision = {}
+        for p in ("tf32x3", "tf32", "fp32"):
+            reps = 1 if p == "fp32" else 10
+            try:
+                f_ms = graph_time(torch, [lambda p=p: fn2.correlation(a, b, *CORR_ARGS, precision=p)], reps, tstream)
+                b_ms = graph_time(torch, [lambda p=p: fn2.correlation_grad(g, a, b, *CORR_ARGS, precision=p)], reps,
+                                  tstream)
+            except Exception as exc:  # pragma: no cover
+                per_precision[p] = {"unavailable": str(exc)[:200]}
+                continue
+            m = executed_mma_flops(B, p) or {}
+            per_precision[p] = {
+                "corr_fwd": op_entry(f_ms, abytes["corr_fwd"], hbm_peak, flops["corr_fwd"], m.get("corr_fwd"), tf32_peak),
+                "corr_bwd": op_entry(b_ms, abytes["corr_bwd"], hbm_peak, flops["corr_bwd"], m.get("corr_bwd"), tf32_peak),
+                "fwd_bwd_hbm_frac": round((abytes["corr_fwd"] + abytes["corr_bwd"]) / ((f_ms + b_ms) * 1e-3) / 1e9
+                                          / hbm_peak, 4),
+                "tolerance": {"tf32x3": "1e-5 rel + 1e-6 abs (the op's fp32 tolerance)",
+                              "tf32": "2.5e-3 of the tensor's max", "fp32": "1e-5 rel + 1e-6 abs"}[p],
+                "what": {"tf32x3": "tcgen05 split-tf32 (the drop-in default)", "tf32": "tcgen05 kind::tf32",
+                         "fp32": "CUDA cores, any geometry"}[p]}
+
     # ---- CPU baseline: the restatement of the reference ops on the host cores, bounded sample ---------------
     cpu = None
+    o = None
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as o
         o.lib()
         ncores = use_all_host_threads()
-        sample = min(B, 16)
+        sample = min(B, REF_SAMPLE)
         data = [x.numpy() for x in host]
         cpu_pass(o, data, 1)
         tc = time.time()
@@ -430,40 +677,106 @@ def main():
                "sample": "%d of the %d pairs, one pass, C restatement of the reference kernels (oracle/fn2_oracle.c), "
                          "OpenMP on %d threads, %.1f s" % (sample, B, ncores, dt)}
 
-    # ---- the reference's own CUDA kernels on this GPU (informational; they are not a CPU path) --------------
+    # ---- BASELINE config 1: ONE pair's correlation forward, warm and cold L2, beside the CPU port ---------------
+    cfg1 = cfg2 = None
+    if extras:
+        a1, b1 = a[:1].contiguous(), b[:1].contiguous()
+        scrub = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+        nb1 = algorithmic_bytes(1)["corr_fwd"]
+        cfg1 = {"workload": "correlation forward, one 512x384 pair at conv3 [1,48,64,256] (11.7 MB: fits the L2)"}
+        for p in ("tf32x3", "tf32"):
+            warm_ms = graph_time(torch, [lambda p=p: fn2.correlation(a1, b1, *CORR_ARGS, precision=p)] * 8, 10, tstream)
+            ts = []
+            with torch.cuda.stream(tstream):
+                for _ in range(12):
+                    scrub.zero_()                      # 256 MB > 126 MB of L2: the pair comes from HBM again
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(tstream)
+                    fn2.correlation(a1, b1, *CORR_ARGS, precision=p)
+                    e1.record(tstream)
+                    torch.cuda.synchronize()
+                    ts.append(e0.elapsed_time(e1))
+            ts.sort()
+            cold_ms = ts[len(ts) // 2]
+            cfg1[p] = {"warm_l2_ms": round(warm_ms, 4), "cold_l2_ms": round(cold_ms, 4),
+                       "warm_pairs_per_s": round(1e3 / warm_ms, 1), "cold_pairs_per_s": round(1e3 / cold_ms, 1),
+                       "cold_hbm_frac": round(nb1 / (cold_ms * 1e-3) / 1e9 / hbm_peak, 4)}
+        if o is not None:
+            an, bn = host[0][:1].numpy(), host[1][:1].numpy()
+            o.c_correlation(an, bn, *CORR_ARGS)
+            tc = time.time()
+            for _ in range(5):
+                o.c_correlation(an, bn, *CORR_ARGS)
+            cfg1["cpu_port_ms"] = round((time.time() - tc) / 5 * 1e3, 2)
+        del scrub
+        # ---- BASELINE config 2: flow_warp + downsample on batch 8, rotating inputs so nothing is found in L2 ----
+        ROT = 6
+        gen = torch.Generator(device=dev).manual_seed(5)
+        IMG = [torch.rand(8, HI, WI, 3, device=dev, generator=gen) for _ in range(ROT)]
+        FLO = [torch.randn(8, HI, WI, 2, device=dev, generator=gen) * 8 for _ in range(ROT)]
+        GI = [torch.randn(8, HI, WI, 3, device=dev, generator=gen) for _ in range(ROT)]
+        ab8 = algorithmic_bytes(8)
+        cfg2 = {"workload": "flow_warp fwd/bwd + downsample on batch-8 512x384 image/flow pairs (%d rotating input "
+                            "sets, 300 MB > L2)" % ROT}
+        for name, mk in (("warp_fwd", lambda i: (lambda: fn2.flow_warp(IMG[i], FLO[i]))),
+                         ("warp_bwd", lambda i: (lambda: fn2.flow_warp_grad(IMG[i], FLO[i], GI[i]))),
+                         ("downsample", lambda i: (lambda: fn2.downsample_multi(FLO[i], DS_SIZES)))):
+            ms = graph_time(torch, [mk(i) for i in range(ROT)], 5, tstream)
+            cfg2[name] = op_entry(ms, ab8[name], hbm_peak)
+        cfg2["pairs_per_s"] = round(8e3 / sum(cfg2[n]["ms"] for n in ("warp_fwd", "warp_bwd", "downsample")), 1)
+        del IMG, FLO, GI
+
+    # ---- the reference's own CUDA kernels on this GPU, per op (they are the reference's only implementation) ----
     ref_gpu = None
     if world == 1 and not args.no_ref_gpu:
         try:
             from oracle import ref
             if ref.available():
-                temps = (torch.empty((B, HC + 40, WC + 40, CC), device=dev), torch.empty((B, HC + 40, WC + 40, CC), device=dev))
-                def ref_step():
-                    ref.correlation(a, b, *CORR_ARGS, temps=temps)
-                    ref.correlation_grad(g, a, b, *CORR_ARGS, temps=temps)
-                    ref.flow_warp(image, flow)
-                    for s in DS_SIZES:
-                        ref.downsample(gt, s)
-                ref_step()
-                torch.cuda.synchronize()
-                tr = time.time()
-                ref_step()
-                torch.cuda.synchronize()
-                dt = time.time() - tr
-                ref_gpu = {"value": B / dt, "unit": "pairs/s", "ms_per_step": dt * 1e3,
-                           "what": "reference src/ops/**.cu.cc kernels compiled unmodified for sm_100a "
-                                   "(oracle/_ref), same batch, without flow_warp backward (broken in the reference)"}
+                temps = (torch.empty((B, HC + 40, WC + 40, CC), device=dev),
+                         torch.empty((B, HC + 40, WC + 40, CC), device=dev))
+                ref_ops = [
+                    ("corr_fwd", lambda: ref.correlation(a, b, *CORR_ARGS, temps=temps)),
+                    ("corr_bwd", lambda: ref.correlation_grad(g, a, b, *CORR_ARGS, temps=temps)),
+                    ("warp_fwd", lambda: ref.flow_warp(image, flow)),
+                    ("warp_bwd", lambda: ref.flow_warp_grad(image, flow, gimg)),
+                    ("downsample", lambda: [ref.downsample(gt, s) for s in DS_SIZES]),
+                ]
+                reps = 5
+                times = {n: [] for n, _ in ref_ops}
+                for r in range(reps + 1):              # first round = warm-up
+                    for n, fn in ref_ops:
+                        torch.cuda.synchronize()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()                    # the reference launches on the legacy default stream,
+                        fn()                           # which is torch's current stream here
+                        e1.record()
+                        torch.cuda.synchronize()
+                        if r > 0:
+                            times[n].append(e0.elapsed_time(e1))
+                med = {n: sorted(v)[len(v) // 2] for n, v in times.items()}
+                total = sum(med.values())
+                ref_gpu = {"value": B / (total * 1e-3), "unit": "pairs/s", "ms_per_step": round(total, 3),
+                           "per_op_ms": {n: round(v, 3) for n, v in med.items()},
+                           "speedup_of_this_library": {n: round(med[n] / per_op_ms[n], 1) for n in med},
+                           "speedup_of_this_library_step": round(total / sum(per_op_ms.values()), 1),
+                           "reps": reps,
+                           "what": "reference src/ops/**.cu.cc kernels compiled unmodified for sm_100a (oracle/_ref), "
+                                   "same batch, CUDA events, median of %d; flow_warp backward through its launcher "
+                                   "(the reference's OpKernel cannot run it: flow_warp_grad.cc:36-37)" % reps}
         except Exception as exc:  # pragma: no cover
             ref_gpu = {"unavailable": str(exc)[:200]}
 
     value = world * B * args.steps / (elapsed_ms / 1e3)
+    cfg = workload_config(B)
     line = {
         "metric": "image_pairs_per_s", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "bf16": "bf16",
-                                                          "tf32x3": "tf32x3"}[precision],
-        "data": "synthetic", "config": workload_config(B, precision), "clocks": clocks, "e2e": e2e,
-        "gpu_launches": int(launches), "roofline": roofline, "per_op": per_op, "cpu_baseline": cpu,
-        "reference_gpu_kernels": ref_gpu,
+        "scaling": "weak", "vs_baseline": None, "dtype": {"fp32": "f32", "tf32": "tf32", "tf32x3": "tf32x3"}[precision],
+        "data": "synthetic", "config": cfg, "correlation_precision": precision,
+        "launch": "CUDA graph replay per op, 5 per step" if graphs else "eager launches",
+        "clocks": clocks, "e2e": e2e, "e2e_copy_ceiling": ceiling,
+        "gpu_launches": int(launches), "roofline": roofline, "per_op": per_op, "per_precision": per_precision,
+        "cpu_baseline": cpu, "cfg1": cfg1, "cfg2": cfg2, "strips4k": strips4k, "reference_gpu_kernels": ref_gpu,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -31,11 +31,14 @@
 // epilogue.
 //
 // fp32-grade mode (X3, FN2_PREC_TF32X3): both operands are split as x = hi + lo (hi = the 19 bits the tensor core
-// reads from a raw fp32 word, lo = x - hi; fn2_tc.cuh x3_lo) and every step issues THREE MMAs into the same
-// accumulator: X.G + X_lo.G + X.G_lo (the lo.lo term, ~2^-21 relative, is dropped).  The builders write G_lo next to
+// reads from a raw fp32 word, lo = x - hi; fn2_tc.cuh x3_lo) and every step issues THREE MMAs: X.G into the main
+// accumulator, X_lo.G + X.G_lo into a second one (the lo.lo term, ~2^-21 relative, is dropped).  The tensor core adds
+// into its fp32 accumulator with truncation, so the error of a sum grows with the number of accumulation steps: the
+// small terms get their own 256 TMEM columns (their rounding is 2^-11 times smaller) and the main accumulator takes
+// a third of the steps; the epilogue adds the two in fp32 on the CUDA cores.  The builders write G_lo next to
 // G from the value they already hold in a register, and convert the TMA-landed X chunk to X_lo in shared memory.  To
 // make room a CTA takes only 128 of the channels (grid x ceil(C/128)): a stage is X 16 KB + X_lo 16 KB + G 32 KB +
-// G_lo 32 KB, two stages, and the accumulator needs 256 TMEM columns.  Results meet the fp32 tolerance
+// G_lo 32 KB, two stages, and each of the two accumulators needs 256 TMEM columns.  Results meet the fp32 tolerance
 // (1e-5 relative + 1e-6 absolute against a float64 evaluation).
 #include <type_traits>
 #include "fn2_tc.cuh"
@@ -158,7 +161,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), X3 ? TILE_N : TMEM_COLS);
+  if (warp == 1) tmem_alloc(smem_u32(&bars->tmem_base), TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -204,9 +207,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
                                        : desc_sw128_kmajor(g_addr + k8 * 32);
             const uint64_t b_lo = mode ? desc_sw128b32_mnmajor(g_addr + GSTAGE + k8 * 1024, GBLOCK, 512)
                                        : desc_sw128_kmajor(g_addr + GSTAGE + k8 * 32);
-            umma_tf32(tmem_base, a_lo, b_hi, idesc, (uint32_t)((it | k8) != 0));   // small terms first
-            umma_tf32(tmem_base, a_hi, b_lo, idesc, 1u);
-            umma_tf32(tmem_base, a_hi, b_hi, idesc, 1u);
+            umma_tf32(tmem_base, a_hi, b_hi, idesc, (uint32_t)((it | k8) != 0));             // main accumulator
+            umma_tf32(tmem_base + TILE_N, a_lo, b_hi, idesc, (uint32_t)((it | k8) != 0));    // small terms
+            umma_tf32(tmem_base + TILE_N, a_hi, b_lo, idesc, 1u);
           }
         } else {
           for (int h = 0; h < P.nhalf; ++h) {
@@ -340,6 +343,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
         if (row >= Hout) continue;  // warp-uniform
         float v[32];
         tmem_ld32(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(h * TILE_N + qq * 32), v);
+        if constexpr (X3) {   // + the accumulator of the small terms, in two pieces (fewer live registers)
+          float w[16];
+          tmem_ld16(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(TILE_N + qq * 32), w);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] += w[j];
+          tmem_ld16(tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)(TILE_N + qq * 32 + 16), w);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[16 + j] += w[j];
+        }
         const uint32_t buf = stg + (uint32_t)(nb & 1) * 4096u;
         if (nb >= 2) {
           if (lane == 0) tma_store_wait_read<1>();
@@ -365,7 +377,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, X3 ? TILE_N : TMEM_COLS);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 

@@ -5,19 +5,22 @@
 // bits (what the tensor core reads from the raw fp32 word anyway) and lo = x - hi (exact, rounded to 11 bits, see
 // fn2_tc.cuh x3_lo), and the products hi*hi, hi*lo, lo*hi and lo*lo are all accumulated in fp32:
 //   <a, b> = <a_hi, b_hi> + <a_hi, b_lo> + <a_lo, b_hi> + <a_lo, b_lo>        error ~2^-21 per product
-// Same banded-Gram formulation as corr_tc.cu (parity classes, 4 b-rows x 32 b-columns per block, TMA zero fill as the
-// op's padding), with the split folded into the MMA shape instead of into extra instructions:
+// Same banded-Gram formulation as corr_tc.cu (parity classes, blocks of b-rows x 32 b-columns -- two rows here --, TMA
+// zero fill as the op's padding), with the split folded into the MMA shape instead of into extra instructions:
 //   * one CTA owns 64 a-pixels (2 class-rows x 32 class-cols).  Its A operand has M = 128 rows: rows 0..63 the raw
 //     pixels, rows 64..127 their lo parts, resident in shared memory for the full K = C (128 KB at C = 256).
-//   * every streamed block of 128 b-pixels becomes N = 256 operand rows: 128 raw + 128 lo.  ONE tcgen05.mma
-//     M128 N256 K8 therefore produces all four partial products at the full-rate shape; they land in four quadrants
-//     of the [128 x 256] accumulator:  lanes 0..63 x cols 0..127 = hi*hi, x cols 128..255 = hi*lo,
-//                                       lanes 64..127 x cols 0..127 = lo*hi, x cols 128..255 = lo*lo.
+//   * every streamed block of 64 b-pixels (2 b-rows) becomes N = 128 operand rows: 64 raw + 64 lo.  ONE tcgen05.mma
+//     M128 N128 K8 therefore produces all four partial products; they land in four quadrants of the [128 x 128]
+//     accumulator:  lanes 0..63 x cols 0..63 = hi*hi, x cols 64..127 = hi*lo,
+//                   lanes 64..127 x cols 0..63 = lo*hi, x cols 64..127 = lo*lo.
+//     A stage of the ring is one 32-channel chunk of a block, 8 KB raw + 8 KB lo: four stages deep, so the TMA fill
+//     and the conversion of the next chunks run under the MMAs of the current one (with 4-row blocks only two 32 KB
+//     stages fit beside the resident a tile and the tensor core waited for every fill: 0.37 ms at N = 32).
 //   * lo parts are made in shared memory by four converter warps (raw chunk -> lo chunk at the same swizzled offset),
 //     so HBM / L2 traffic is that of the plain kernel: nothing is pre-split in global memory, no workspace.
 //   * epilogue: a warp can only read its own TMEM lane quadrant, so the warp holding a pixel row's hi lanes and the
 //     one holding its lo lanes each add their two column halves, exchange one partial through the staging tile and
-//     each finishes (transpose + coalesced 441-channel store) one b-row of every pair of b-rows they share.
+//     each finishes (transpose + coalesced 441-channel store) one of the block's two b-rows.
 // Cost: 4x the tensor work of the tf32 kernel per output, for an output that meets the fp32 tolerance
 // (1e-5 relative + 1e-6 absolute against a float64 evaluation).
 //
@@ -35,11 +38,12 @@ constexpr int XR = 2;                   // a-rows per tile (class space)
 constexpr int TILE_C = 32;              // a-cols per tile
 constexpr int A_HALF = 64 * 128;        // 64 a-pixels x 32 channels fp32 = 8 KB (raw; the lo copy follows it)
 constexpr int A_CHUNK = 2 * A_HALF;     // M = 128 operand rows of one 32-channel chunk
-constexpr int B_HALF = 128 * 128;       // 128 b-pixels x 32 channels = 16 KB (raw; the lo copy follows it)
-constexpr int B_STAGE = 2 * B_HALF;     // N = 256 operand rows of one 32-channel chunk
-constexpr int NSTAGE = 2;               // B ring depth
-constexpr int NBUF = 2;                 // TMEM accumulator buffers (2 x 256 columns = 512)
-constexpr int BUF_COLS = 256;
+constexpr int BROWS = 2;                // b-rows per block
+constexpr int B_HALF = BROWS * 32 * 128;   // 64 b-pixels x 32 channels = 8 KB (raw; the lo copy follows it)
+constexpr int B_STAGE = 2 * B_HALF;     // N = 128 operand rows of one 32-channel chunk
+constexpr int NSTAGE = 4;               // B ring depth
+constexpr int NBUF = 4;                 // TMEM accumulator buffers (4 x 128 columns = 512)
+constexpr int BUF_COLS = 2 * BROWS * 32;
 constexpr int MAX_KC = 8;               // C <= 256
 constexpr int NEPI = 4;                 // epilogue warps: (a-row, hi/lo lanes) = one per TMEM lane quadrant
 constexpr int NCONV = 4;                // converter warps
@@ -48,7 +52,7 @@ constexpr int STG_FLOATS = 32 * 33;     // transposed staging tile [b column][a 
 
 struct X3Params {
   CUtensorMap a[4];   // per parity class, boxes of 2 rows x 32 cols x 32 channels
-  CUtensorMap b[4];   // per parity class, boxes of 4 rows x 32 cols x 32 channels
+  CUtensorMap b[4];   // per parity class, boxes of 2 rows x 32 cols x 32 channels
   float* out;
   int N, H, W, C, D, s2, ncls;
   int Hc[2], Wc[2];   // class-space extent per parity
@@ -62,8 +66,8 @@ struct X3Params {
 };
 
 struct __align__(8) X3Barriers {
-  uint64_t a_full;            // TMA: the raw a tile has landed
-  uint64_t a_conv;            // converters: its lo half is written
+  uint64_t a_full[MAX_KC];    // TMA: chunk kc of the raw a tile has landed
+  uint64_t a_conv[MAX_KC];    // converters: its lo half is written (block 0 starts on chunk 0, not on the whole tile)
   uint64_t full[NSTAGE];      // TMA: raw b chunk landed
   uint64_t conv[NSTAGE];      // converters: lo b chunk written
   uint64_t empty[NSTAGE];     // MMAs have read the stage
@@ -78,21 +82,22 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 
 // 32 lanes x 32 columns of BOTH column halves of an accumulator buffer, summed: (x raw b) + (x lo b)
 __device__ __forceinline__ void tmem_ld32_sum2(uint32_t taddr, float (&v)[32]) {
+  constexpr uint32_t LO = BUF_COLS / 2;
   float w[16];   // the second half in two pieces: fewer live registers
   tmem_ld32(taddr, v);
-  tmem_ld16(taddr + 128u, w);
+  tmem_ld16(taddr + LO, w);
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[j] += w[j];
-  tmem_ld16(taddr + 144u, w);
+  tmem_ld16(taddr + LO + 16u, w);
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[16 + j] += w[j];
 }
 
-// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 32 KB][staging: NEPI x 32x33 floats][barriers]
+// Dynamic shared memory: [A: nkc x 16 KB][B ring: NSTAGE x 16 KB][staging: NEPI x 32x33 floats][barriers]
 template <int R, bool WIDE>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __grid_constant__ X3Params P) {
   constexpr int GW = 2 * R + 1;
-  constexpr int NHX = WIDE ? 2 : 1;                 // 32-column b blocks per group of 4 b-rows
+  constexpr int NHX = WIDE ? 2 : 1;                 // 32-column b blocks per group of BROWS b-rows
   constexpr int XO0 = WIDE ? -16 : 0;               // column origin of the first one, relative to the a tile
   constexpr int NTT = WIDE ? (GW * 16 + 31) / 32 : GW;  // store instructions per (a-row, b-row, block)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -117,12 +122,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
   const int Hcb = P.Hcb[cy];
   const int s_first = max(0, y0 + P.boff - R);
   const int s_last = min(Hcb - 1, y0 + P.boff + XR - 1 + R);
-  const int nblk = max(0, (s_last - s_first + 1 + 3) / 4) * NHX;   // blocks of 4 b-rows x 32 b-columns
+  const int nblk = max(0, (s_last - s_first + BROWS) / BROWS) * NHX;   // blocks of BROWS b-rows x 32 b-columns
   const int nkc = P.nkc;
 
   if (threadIdx.x == 0) {
-    mbar_init(smem_u32(&bars->a_full), 1);
-    mbar_init(smem_u32(&bars->a_conv), NCONV);
+    for (int i = 0; i < MAX_KC; ++i) {
+      mbar_init(smem_u32(&bars->a_full[i]), 1);
+      mbar_init(smem_u32(&bars->a_conv[i]), NCONV);
+    }
     for (int i = 0; i < NSTAGE; ++i) {
       mbar_init(smem_u32(&bars->full[i]), 1);
       mbar_init(smem_u32(&bars->conv[i]), NCONV);
@@ -141,13 +148,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (elect_one()) {
-      const uint32_t a_full = smem_u32(&bars->a_full);
-      mbar_expect_tx(a_full, (uint32_t)nkc * A_HALF);
-      for (int kc = 0; kc < nkc; ++kc)
+      for (int kc = 0; kc < nkc; ++kc) {
+        const uint32_t a_full = smem_u32(&bars->a_full[kc]);
+        mbar_expect_tx(a_full, A_HALF);
         tma_load_4d(smem_u32(sA + (size_t)kc * A_CHUNK), &P.a[cls], a_full, kc * KCH, x0, y0, n);
+      }
       int it = 0;
       for (int blk = 0; blk < nblk; ++blk) {
-        const int srow = s_first + (blk / NHX) * 4;
+        const int srow = s_first + (blk / NHX) * BROWS;
         const int xcol = x0 + XO0 + (blk % NHX) * 32;
         for (int kc = 0; kc < nkc; ++kc, ++it) {
           const int stage = it % NSTAGE;
@@ -162,11 +170,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
     // ================================ MMA issuer ================================
     if (elect_one()) {
       constexpr uint32_t idesc = idesc_tf32(128, BUF_COLS);
-      if (nblk > 0) {
-        mbar_wait(smem_u32(&bars->a_full), 0);
-        mbar_wait(smem_u32(&bars->a_conv), 0);
-        tc_fence_after();
-      }
       int it = 0;
       for (int blk = 0; blk < nblk; ++blk) {
         const int buf = blk % NBUF;
@@ -176,6 +179,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
         for (int kc = 0; kc < nkc; ++kc, ++it) {
           const int stage = it % NSTAGE;
           const uint32_t par = (it / NSTAGE) & 1;
+          if (blk == 0) {   // the a tile arrives and is split chunk by chunk
+            mbar_wait(smem_u32(&bars->a_full[kc]), 0);
+            mbar_wait(smem_u32(&bars->a_conv[kc]), 0);
+          }
           mbar_wait(smem_u32(&bars->full[stage]), par);
           mbar_wait(smem_u32(&bars->conv[stage]), par);
           tc_fence_after();
@@ -195,8 +202,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
     const int q = warp & 3;              // TMEM lane quadrant this warp may read
     const int ar = q & 1;                // a-row of the tile
     const int isLo = q >> 1;             // quadrants 2, 3 hold the products of a_lo
-    // The hi warp and the lo warp of an a-row share two staging tiles.  Of the b-rows (half, half + 2) of a block,
-    // tile 0 collects b-row `half` (finished by the hi warp), tile 1 b-row `half + 2` (finished by the lo warp).
+    // The hi warp and the lo warp of an a-row share two staging tiles: tile 0 collects b-row 0 of a block (finished
+    // by the hi warp), tile 1 b-row 1 (finished by the lo warp).
     float* mine = sStage + (ar * 2 + isLo) * STG_FLOATS;
     float* theirs = sStage + (ar * 2 + (isLo ^ 1)) * STG_FLOATS;
     const int y = y0 + ar;               // class-space row of this warp's 32 pixels
@@ -258,11 +265,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
         const int buf = blk % NBUF;
         mbar_wait(smem_u32(&bars->tmem_full[buf]), (blk / NBUF) & 1);
         tc_fence_after();
-        const int sbase = s_first + (blk0 / NHX) * 4;
+        const int sbase = s_first + (blk0 / NHX) * BROWS;
         const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BUF_COLS);
-#pragma unroll 1
-        for (int half = 0; half < 2; ++half) {
-          const int brMine = half + 2 * isLo, brTheirs = half + 2 * (isLo ^ 1);
+        {
+          const int brMine = isLo, brTheirs = isLo ^ 1;
           const int sM = sbase + brMine, sT = sbase + brTheirs;
           const int pM = sM - (y + P.boff), pT = sT - (y + P.boff);
           const bool okM = row_ok && pM >= -R && pM <= R && sM < Hcb;   // the same in both warps of the pair
@@ -302,19 +308,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
     // ================================ converters (warps 6..9): lo = x - tf32(x) ================================
     const int ct = threadIdx.x - (64 + 32 * NEPI);
     constexpr int NCT = 32 * NCONV;
-    mbar_wait(smem_u32(&bars->a_full), 0);
     for (int kc = 0; kc < nkc; ++kc) {
+      mbar_wait(smem_u32(&bars->a_full[kc]), 0);
       uint8_t* base = sA + (size_t)kc * A_CHUNK;
+      float4 v[A_HALF / 16 / NCT];
 #pragma unroll
-      for (int i = 0; i < A_HALF / 16 / NCT; ++i) {
-        const int off = (ct + i * NCT) * 16;
-        const float4 v = *reinterpret_cast<const float4*>(base + off);
-        *reinterpret_cast<float4*>(base + A_HALF + off) = x3_lo4(v);
-      }
+      for (int i = 0; i < A_HALF / 16 / NCT; ++i) v[i] = *reinterpret_cast<const float4*>(base + (ct + i * NCT) * 16);
+#pragma unroll
+      for (int i = 0; i < A_HALF / 16 / NCT; ++i)
+        *reinterpret_cast<float4*>(base + A_HALF + (ct + i * NCT) * 16) = x3_lo4(v[i]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&bars->a_conv[kc]));
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
-    __syncwarp();
-    if (lane == 0) mbar_arrive(smem_u32(&bars->a_conv));
     const int nit = nblk * nkc;
     for (int it = 0; it < nit; ++it) {
       const int stage = it % NSTAGE;
@@ -370,7 +376,7 @@ int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float*
       continue;
     }
     if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, XR) ||
-        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, 4))
+        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, BROWS))
       return FN2_E_CUDA;
   }
   for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }

@@ -94,32 +94,37 @@ __host__ __device__ inline BandSmem band_smem_layout(int nwarps, int px, int nv,
 }
 
 // ---------------------------------------------------------------------------------------------------- tables
-__global__ void ms_tables_kernel(MsParams p, float* __restrict__ ws) {
+// grid (TBX, ns): blockIdx.y = scale; the entries of a scale are independent, each on its own thread (rows, columns,
+// ranges) or its own warp (total weights), so the kernel is as long as ONE entry's chain of IEEE divisions.
+constexpr int TBX = 24;
+__global__ void __launch_bounds__(256) ms_tables_kernel(MsParams p, float* __restrict__ ws) {
   int* wi = reinterpret_cast<int*>(ws);
+  const int s = blockIdx.y;
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
   const int gthreads = gridDim.x * blockDim.x;
   const int gwarp = gtid >> 5, gwarps = gthreads >> 5, lane = threadIdx.x & 31;
-  if (gtid == 0) *reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + p.ctrlOff) = 0u;   // combine ticket
-  for (int s = 0; s < p.ns; ++s) {
-    const int oH = p.oH[s], oW = p.oW[s];
-    const float hs = p.hs[s], wsc = p.ws[s];
-    // one thread per input row / input column
-    for (int y = gtid; y < p.iH; y += gthreads) {
+  if (gtid == 0 && s == 0) *reinterpret_cast<unsigned*>(reinterpret_cast<char*>(ws) + p.ctrlOff) = 0u;   // combine ticket
+  const int oH = p.oH[s], oW = p.oW[s];
+  const float hs = p.hs[s], wsc = p.ws[s];
+  // task space: [0, iH) input rows, then iW input columns, then oW + 1 column starts, then oH output rows
+  const int ntask = p.iH + p.iW + (oW + 1) + oH;
+  for (int task = gtid; task < ntask; task += gthreads) {
+    if (task < p.iH) {
+      const int y = task;
       const int d = last_centre_le(y, hs, oH, p.iH);
       const float a = tri((float)y, src_pos(d, oH - 1, p.iH - 1), hs);
       const float b = d + 1 < oH ? tri((float)y, src_pos(d + 1, oH - 1, p.iH - 1), hs) : 0.f;
       reinterpret_cast<float2*>(ws + p.t.rowW[s])[y] = make_float2(a, b);
       wi[p.t.rowD[s] + y] = d;
-    }
-    for (int x = gtid; x < p.iW; x += gthreads) {
+    } else if (task < p.iH + p.iW) {
+      const int x = task - p.iH;
       const int d = last_centre_le(x, wsc, oW, p.iW);
       const float a = tri((float)x, src_pos(d, oW - 1, p.iW - 1), wsc);
       const float b = d + 1 < oW ? tri((float)x, src_pos(d + 1, oW - 1, p.iW - 1), wsc) : 0.f;
       reinterpret_cast<float2*>(ws + p.t.colW[s])[x] = make_float2(a, b);
       wi[p.t.colD[s] + x] = d;
-    }
-    // one thread per output row / column: ranges
-    for (int dx = gtid; dx <= oW; dx += gthreads) {
+    } else if (task < p.iH + p.iW + oW + 1) {
+      const int dx = task - p.iH - p.iW;
       wi[p.t.colS[s] + dx] = dx == 0 ? 0 : (dx == oW ? p.iW : (int)ceilf(src_pos(dx, oW - 1, p.iW - 1)));
       if (dx < oW) {
         // strip w feeds dx iff dlo(first px) <= dx and dlo(last px) >= dx - 1   (dlo(x) >= d  <=>  x >= centre(d))
@@ -128,26 +133,27 @@ __global__ void ms_tables_kernel(MsParams p, float* __restrict__ ws) {
         reinterpret_cast<int2*>(wi + p.t.warpR[s])[dx] =
             make_int2(min(xlo, p.iW - 1) / p.pxw, min(max(xhi, 0), p.iW - 1) / p.pxw);
       }
-    }
-    for (int dy = gtid; dy < oH; dy += gthreads) {
+    } else {
+      const int dy = task - p.iH - p.iW - oW - 1;
       const int ylo = dy >= 2 ? (int)ceilf(src_pos(dy - 1, oH - 1, p.iH - 1)) : 0;
       const int yhi = dy + 1 < oH ? (int)ceilf(src_pos(dy + 1, oH - 1, p.iH - 1)) - 1 : p.iH - 1;
       reinterpret_cast<int2*>(wi + p.t.bandR[s])[dy] =
           make_int2(min(ylo, p.iH - 1) / RB, min(max(yhi, 0), p.iH - 1) / RB);
     }
-    // one warp per output row / column: total weights (lane-strided, then a fixed tree)
-    for (int e = gwarp; e < oH + oW; e += gwarps) {
-      const bool isx = e >= oH;
-      const int d = isx ? e - oH : e;
-      const int on = isx ? oW : oH, in_ = isx ? p.iW : p.iH;
-      const float sc = isx ? wsc : hs;
-      const float c = src_pos(d, on - 1, in_ - 1);
-      const int lo = max(0, (int)floorf(c - sc)), hi = min(in_ - 1, (int)ceilf(c + sc));
-      float t = 0.f;
-      for (int i = lo + lane; i <= hi; i += 32) t += tri((float)i, c, sc);
-      for (int off = 16; off >= 1; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
-      if (lane == 0) ws[(isx ? p.t.totX[s] : p.t.totY[s]) + d] = t;
-    }
+  }
+  // one warp per output row / column: total weights (lane-strided, then a fixed tree); warps taken from the END of the
+  // grid so they are not the ones busy with the entries above
+  for (int e = gwarps - 1 - gwarp; e < oH + oW; e += gwarps) {
+    const bool isx = e >= oH;
+    const int d = isx ? e - oH : e;
+    const int on = isx ? oW : oH, in_ = isx ? p.iW : p.iH;
+    const float sc = isx ? wsc : hs;
+    const float c = src_pos(d, on - 1, in_ - 1);
+    const int lo = max(0, (int)floorf(c - sc)), hi = min(in_ - 1, (int)ceilf(c + sc));
+    float t = 0.f;
+    for (int i = lo + lane; i <= hi; i += 32) t += tri((float)i, c, sc);
+    for (int off = 16; off >= 1; off >>= 1) t += __shfl_xor_sync(FULL, t, off);
+    if (lane == 0) ws[(isx ? p.t.totX[s] : p.t.totY[s]) + d] = t;
   }
 }
 
@@ -191,6 +197,13 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
   float* stage = reinterpret_cast<float*>(sm + L.stage);     // per warp: strips A and B, [pxw][NV] each
   float4* nanw = reinterpret_cast<float4*>(sm + L.nanw) + tid;   // [MS][2][nthr]: this thread's NaN-weight sums
 
+  // the first rows are requested before anything else so that their latency overlaps the table copy
+  const int x0 = tid * PX;
+  const float* col = in + ((size_t)n * p.iH * p.iW + (size_t)min(x0, p.iW - PX)) * CT;
+  float4 v[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(yb + u, ye) * p.iW * CT));
+
   // ---- this band's slice of the tables ----
   for (int idx = tid; idx < MS * RB; idx += nthr) {
     const int s = idx / RB, i = idx - s * RB;
@@ -202,9 +215,18 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
     }
     rowW[idx] = w; rowD[idx] = d;
   }
-  for (int idx = tid; idx < MS * ncols; idx += nthr) {
-    const int s = idx / ncols, x = idx - s * ncols;
-    colW[idx] = (s < p.ns && x < p.iW) ? reinterpret_cast<const float2*>(ws + p.t.colW[s])[x] : make_float2(0.f, 0.f);
+  {   // every thread fetches the x-weights of its own PX pixels for all scales: MS independent 16-byte-class loads
+    float2 cwv[MS][PX];
+#pragma unroll
+    for (int s = 0; s < MS; ++s)
+#pragma unroll
+      for (int q = 0; q < PX; ++q)
+        cwv[s][q] = (s < p.ns && x0 + q < p.iW) ? __ldg(reinterpret_cast<const float2*>(ws + p.t.colW[s]) + x0 + q)
+                                                : make_float2(0.f, 0.f);
+#pragma unroll
+    for (int s = 0; s < MS; ++s)
+#pragma unroll
+      for (int q = 0; q < PX; ++q) colW[s * ncols + x0 + q] = cwv[s][q];
   }
   for (int i = tid; i < cswords; i += nthr) colS[i] = wsi[p.t.colS[0] + i];
   if (lane < MS) {
@@ -303,15 +325,14 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
     for (int k = 0; k < 2; ++k)
 #pragma unroll
       for (int f = 0; f < 4; ++f) av[s][k][f] = 0.f;
-  const int x0 = tid * PX;
-  const float* col = in + ((size_t)n * p.iH * p.iW + (size_t)min(x0, p.iW - PX)) * CT;
   const float scale = p.in_scale;
 
   for (int y0 = yb; y0 <= ye; y0 += U) {
-    float4 v[U];
+    if (y0 > yb) {
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(y0 + u, ye) * p.iW * CT));
+      for (int u = 0; u < U; ++u)
+        v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(y0 + u, ye) * p.iW * CT));
+    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       if (y0 + u <= ye) {                                  // uniform
@@ -417,7 +438,10 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
     for (int c = 0; c < CT; ++c) {
       const float nanw = acc[CT + c];                        // accum_nan
       const float wgt = tot - nanw;                          // accum_weight: the samples that are not NaN
-      const float r = (nanw / wgt > 0.5f) ? nan_f() : acc[c] / wgt;   // :72-76
+      // :72-76.  accum_nan / accum_weight > 0.5 means accum_weight < 2/3 of the total, far from the cancellation in
+      // `tot - nanw`; when (nearly) every sample is NaN the difference is rounding noise around 0 (the reference has
+      // an exact 0 there and divides by it): <= 0 is NaN too.
+      const float r = (wgt <= 0.f || nanw / wgt > 0.5f) ? nan_f() : acc[c] / wgt;
       if (p.out[s]) p.out[s][o + c] = r;
       if (p.pred[s]) {
         diff[c] = p.pred[s][o + c] - r;
@@ -532,7 +556,7 @@ int ms_launch(const MsParams& p, size_t band_smem, const float* in, void* ws, cu
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
   float* w = static_cast<float*>(ws);
-  ms_tables_kernel<<<16, 256, 0, st>>>(p, w);
+  ms_tables_kernel<<<dim3(TBX, (unsigned)p.ns), 256, 0, st>>>(p, w);
   int rc = after_launch();
   if (rc != FN2_OK) return rc;
   ms_band_kernel<CT><<<dim3((unsigned)p.nbands, (unsigned)p.N), p.nwarps * 32, band_smem, st>>>(p, in, w);

@@ -125,8 +125,8 @@ def test_multiscale_epe_matches_the_graph_nodes(C, scale):
     pd = [p.cuda().requires_grad_() for p in preds]
     epe, downs = fn2.multiscale_epe(x.cuda(), pd, scale, return_downsampled=True)
     np.testing.assert_allclose(epe.detach().cpu().numpy(), want, rtol=2e-5)
-    for d, w in zip(downs, wdowns):
-        assert_close(d.cpu().numpy(), w, rel=1e-5, abs_=5e-6, what="downsampled in the fused loss")
+    for d, w in zip(downs, wdowns):   # absolute part scales with the data (samples are 5 * scale in magnitude)
+        assert_close(d.cpu().numpy(), w, rel=1e-5, abs_=5e-6 * max(1.0, scale), what="downsampled in the fused loss")
     # gradient w.r.t. the predictions = autograd through the same formula on the kernel's downsampled tensors
     wts = torch.tensor([0.32, 0.08, 0.02, 0.01, 0.005], device="cuda")
     (epe * wts).sum().backward()

@@ -47,7 +47,8 @@ def _worker(rank, world, port, H, W, C, outdir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,H", [(2, 44), (3, 66), (2, 41)])
+@pytest.mark.parametrize("world,H", [(2, 44), (3, 66), (2, 41),      # strips shorter than 2 halos: exchange, then one call
+                                     (2, 100), (3, 150)])             # interior rows computed under the exchange
 def test_strips_reproduce_whole_image_op(tmp_path, world, H):
     from oracle import oracle as o
     W, C = 10, 4
