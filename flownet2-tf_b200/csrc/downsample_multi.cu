@@ -37,31 +37,34 @@ namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MS = 5;     // scales per launch (the reference's losses use five, flownet_c.py:135-160)
-constexpr int RB = 16;    // input rows per band
+constexpr int RB = 16;    // input rows per band: fixed, so the summation order never depends on the batch size
 constexpr int U = 4;      // rows in flight per thread
 constexpr int CB = 256;   // threads of the combine kernel
+constexpr int NSLOT = 2 * MS;   // staged rows: two groups of MS used alternately, all of them by the band's last flush
+#ifndef DS_MINB
+#define DS_MINB 2
+#endif
+static_assert(RB * 4 <= 64, "one NaN bit per (row, float) of a thread in a 64-bit word");
 
 // Offsets (4-byte words) of the per-scale tables inside the workspace.
 struct MsTables {
   int rowW[MS];    // [iH] float2: weight of input row y towards output rows dlo(y), dlo(y) + 1
   int rowD[MS];    // [iH] int: dlo(y)
   int colW[MS];    // [iW] float2: the same along x
-  int colD[MS];    // [iW] int
   int colS[MS];    // [oW + 1] int: first input column whose nearest-left output column is dx
   int totX[MS];    // [oW] float: sum of the x-weights of output column dx
   int totY[MS];    // [oH] float
   int bandR[MS];   // [oH] int2: first / last band that feeds output row dy
-  int warpR[MS];   // [oW] int2: first / last warp strip that feeds output column dx
   int words;       // size of the table area
 };
 
 struct MsParams {
   int N, iH, iW, ns;
-  int nbands, nwarps, pxw;        // bands per image, warp strips per row, input pixels per warp strip
+  int nbands, nthr;               // bands per image, threads of a band CTA (a multiple of 32)
   int oH[MS], oW[MS];
-  int maxRows[MS], maxCols[MS];   // output rows a band / output columns a warp strip can touch
-  int J[MS];                      // lanes that share one output column in the horizontal pass
-  int pOff[MS], pTile;            // partial entries: offset of scale s inside a tile, entries per tile
+  int maxRows[MS];                // output rows a band can touch
+  int J[MS];                      // lanes that share one output column in the horizontal pass (a power of two <= 32)
+  int pOff[MS], pTile;            // partial entries: offset of scale s inside a band's tile, entries per tile
   int blkOff[MS + 1];             // combine kernel: first block of scale s within an image
   float hs[MS], ws[MS];
   float in_scale;                 // samples are multiplied by this on load (the loss's flow * 0.05), 1 = none
@@ -75,20 +78,19 @@ struct MsParams {
 
 // Shared-memory layout of the band kernel (bytes, every area 16-byte aligned); used by the host for the launch size.
 struct BandSmem {
-  size_t rowW, rowD, fmask, wcol, colW, colS, stage, nanw, total;
+  size_t rowW, rowD, fmask, colS, colW, stage, nstage, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline BandSmem band_smem_layout(int nwarps, int px, int nv, int cswords) {
+__host__ __device__ inline BandSmem band_smem_layout(int nthr, int iW, int cswords) {
   BandSmem L;
   size_t o = 0;
   L.rowW = o; o = up16(o + (size_t)MS * RB * 8);
   L.rowD = o; o = up16(o + (size_t)MS * RB * 4);
   L.fmask = o; o = up16(o + (size_t)RB * 4);
-  L.wcol = o; o = up16(o + (size_t)nwarps * MS * 2 * 4);
-  L.colW = o; o = up16(o + (size_t)MS * nwarps * 32 * px * 8);
   L.colS = o; o = up16(o + (size_t)cswords * 4);
-  L.stage = o; o = up16(o + (size_t)nwarps * 2 * (32 * px) * nv * 4);
-  L.nanw = o; o = up16(o + (size_t)MS * 2 * nwarps * 32 * 16);
+  L.colW = o; o = up16(o + (size_t)MS * iW * 8);
+  L.stage = o; o = up16(o + (size_t)NSLOT * nthr * 16);
+  L.nstage = o; o = up16(o + (size_t)nthr * 16);
   L.total = o;
   return L;
 }
@@ -122,18 +124,11 @@ __global__ void __launch_bounds__(256) ms_tables_kernel(MsParams p, float* __res
       const float a = tri((float)x, src_pos(d, oW - 1, p.iW - 1), wsc);
       const float b = d + 1 < oW ? tri((float)x, src_pos(d + 1, oW - 1, p.iW - 1), wsc) : 0.f;
       reinterpret_cast<float2*>(ws + p.t.colW[s])[x] = make_float2(a, b);
-      wi[p.t.colD[s] + x] = d;
     } else if (task < p.iH + p.iW + oW + 1) {
       const int dx = task - p.iH - p.iW;
       wi[p.t.colS[s] + dx] = dx == 0 ? 0 : (dx == oW ? p.iW : (int)ceilf(src_pos(dx, oW - 1, p.iW - 1)));
-      if (dx < oW) {
-        // strip w feeds dx iff dlo(first px) <= dx and dlo(last px) >= dx - 1   (dlo(x) >= d  <=>  x >= centre(d))
-        const int xlo = dx >= 2 ? (int)ceilf(src_pos(dx - 1, oW - 1, p.iW - 1)) : 0;
-        const int xhi = dx + 1 < oW ? (int)ceilf(src_pos(dx + 1, oW - 1, p.iW - 1)) - 1 : p.iW - 1;
-        reinterpret_cast<int2*>(wi + p.t.warpR[s])[dx] =
-            make_int2(min(xlo, p.iW - 1) / p.pxw, min(max(xhi, 0), p.iW - 1) / p.pxw);
-      }
     } else {
+      // band b feeds dy iff it holds a row y with dlo(y) in {dy - 1, dy}   (dlo(y) >= d  <=>  y >= centre(d))
       const int dy = task - p.iH - p.iW - oW - 1;
       const int ylo = dy >= 2 ? (int)ceilf(src_pos(dy - 1, oH - 1, p.iH - 1)) : 0;
       const int yhi = dy + 1 < oH ? (int)ceilf(src_pos(dy + 1, oH - 1, p.iH - 1)) - 1 : p.iH - 1;
@@ -169,76 +164,65 @@ __device__ __forceinline__ void add_entry(float (&acc)[NV], const float* e) {
 }
 
 // ------------------------------------------------------------------------------------------------- band walk
-// CT channels; a thread owns PX = 4 / CT adjacent pixels (one float4 per row).
-template <int CT>
-__global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float* __restrict__ in,
-                                                         float* __restrict__ ws) {
+// grid (bands of RB input rows) x (images); CT channels; a thread owns the 4 floats (PX = 4 / CT adjacent pixels) of one
+// 16-byte column slot and walks the band's rows downwards, U rows in flight, reading every input byte exactly once.
+// The weight is separable, w = wx(x) * wy(y), and an input row feeds at most two output rows of every scale (the last
+// centre at or above it, and the next one): per scale the thread keeps the VERTICAL sums of those two live output rows
+// of its 4 floats in registers (2 FMAs per float, scale and row).  When the walk passes the centre of the next output
+// row of some scales (a block-uniform event, fmask) the finished rows are parked in shared memory -- one 16-byte store
+// per thread and row --, ONE block barrier follows, and the whole CTA sums each parked row horizontally: J lanes share
+// an output column, each adds its share of the column's window in a fixed order (x-weights from a shared copy of the
+// table), a fixed shuffle tree joins the J partial sums, and the band's partial output row goes to the caller's
+// workspace (it stays in L2).  Parked rows alternate between two groups of slots, so no second barrier is needed.
+// NaN samples are rare: the walk only records WHERE they were (one bit per row and float); the barrier of a flush also
+// tells whether any thread of the CTA has met one (__syncthreads_or), and only then the NaN weights of the parked rows
+// are rebuilt from the bits (same additions, same order as a running sum) and summed like the values.
+template <int CT, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) ms_band_kernel(MsParams p, const float* __restrict__ in,
+                                                             float* __restrict__ ws) {
   constexpr int PX = 4 / CT;
-  constexpr int NV = 2 * CT;                    // per pixel: value and NaN-weight sums per channel
+  constexpr int NV = 2 * CT;                    // per output pixel: value and NaN-weight sums per channel
   extern __shared__ __align__(16) uint8_t sm[];
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int lane = tid & 31;
   const int band = blockIdx.x, n = blockIdx.y;
   const int yb = band * RB, ye = min(p.iH - 1, yb + RB - 1);
   const int nrows = ye - yb + 1;
-  const int ncols = nthr * PX;
-  const int pxw = 32 * PX;
+  const int iW = p.iW;
   const int* wsi = reinterpret_cast<const int*>(ws);
 
   // the colS tables are packed back to back in the workspace and followed by totX[0]
   const int cswords = p.t.totX[0] - p.t.colS[0];
-  const BandSmem L = band_smem_layout(nthr >> 5, PX, NV, cswords);
+  const BandSmem L = band_smem_layout(nthr, iW, cswords);
   float2* rowW = reinterpret_cast<float2*>(sm + L.rowW);     // [MS][RB]
   int* rowD = reinterpret_cast<int*>(sm + L.rowD);           // [MS][RB]
   int* fmask = reinterpret_cast<int*>(sm + L.fmask);         // [RB] bit s: scale s finishes an output row before row i
-  int* wcol = reinterpret_cast<int*>(sm + L.wcol);           // [nwarps][MS][2] first / last output column of a strip
-  float2* colW = reinterpret_cast<float2*>(sm + L.colW);     // [MS][ncols]
   int* colS = reinterpret_cast<int*>(sm + L.colS);           // per scale [oW + 1], packed
-  float* stage = reinterpret_cast<float*>(sm + L.stage);     // per warp: strips A and B, [pxw][NV] each
-  float4* nanw = reinterpret_cast<float4*>(sm + L.nanw) + tid;   // [MS][2][nthr]: this thread's NaN-weight sums
+  float2* colW = reinterpret_cast<float2*>(sm + L.colW);     // [MS][iW]
+  float4* stage = reinterpret_cast<float4*>(sm + L.stage);   // [NSLOT][nthr]: parked rows of vertical sums
+  float4* nstage = reinterpret_cast<float4*>(sm + L.nstage); // [nthr]: NaN weights of one parked row (rare path)
 
   // the first rows are requested before anything else so that their latency overlaps the table copy
   const int x0 = tid * PX;
-  const float* col = in + ((size_t)n * p.iH * p.iW + (size_t)min(x0, p.iW - PX)) * CT;
+  const float* col = in + ((size_t)n * p.iH * iW + (size_t)min(x0, iW - PX)) * CT;
   float4 v[U];
 #pragma unroll
-  for (int u = 0; u < U; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(yb + u, ye) * p.iW * CT));
+  for (int u = 0; u < U; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(yb + u, ye) * iW * CT));
 
-  // ---- this band's slice of the tables ----
+  // ---- this band's slice of the row tables, the column tables ----
   for (int idx = tid; idx < MS * RB; idx += nthr) {
     const int s = idx / RB, i = idx - s * RB;
     float2 w = make_float2(0.f, 0.f);
     int d = 0;
     if (s < p.ns && i < nrows) {
-      w = reinterpret_cast<const float2*>(ws + p.t.rowW[s])[yb + i];
-      d = wsi[p.t.rowD[s] + yb + i];
+      w = __ldg(reinterpret_cast<const float2*>(ws + p.t.rowW[s]) + yb + i);
+      d = __ldg(wsi + p.t.rowD[s] + yb + i);
     }
     rowW[idx] = w; rowD[idx] = d;
   }
-  {   // every thread fetches the x-weights of its own PX pixels for all scales: MS independent 16-byte-class loads
-    float2 cwv[MS][PX];
-#pragma unroll
-    for (int s = 0; s < MS; ++s)
-#pragma unroll
-      for (int q = 0; q < PX; ++q)
-        cwv[s][q] = (s < p.ns && x0 + q < p.iW) ? __ldg(reinterpret_cast<const float2*>(ws + p.t.colW[s]) + x0 + q)
-                                                : make_float2(0.f, 0.f);
-#pragma unroll
-    for (int s = 0; s < MS; ++s)
-#pragma unroll
-      for (int q = 0; q < PX; ++q) colW[s * ncols + x0 + q] = cwv[s][q];
-  }
-  for (int i = tid; i < cswords; i += nthr) colS[i] = wsi[p.t.colS[0] + i];
-  if (lane < MS) {
-    const int s = lane;
-    const int wx0 = warp * pxw, wx1 = min(wx0 + pxw, p.iW);
-    int cf = 0, cl = -1;
-    if (s < p.ns && wx0 < p.iW) {
-      cf = wsi[p.t.colD[s] + wx0];
-      cl = min(p.oW[s] - 1, wsi[p.t.colD[s] + wx1 - 1] + 1);
-    }
-    wcol[(warp * MS + s) * 2] = cf; wcol[(warp * MS + s) * 2 + 1] = cl;
-  }
+  for (int s = 0; s < p.ns; ++s)
+    for (int x = tid; x < iW; x += nthr) colW[s * iW + x] = __ldg(reinterpret_cast<const float2*>(ws + p.t.colW[s]) + x);
+  for (int i = tid; i < cswords; i += nthr) colS[i] = __ldg(wsi + p.t.colS[0] + i);
   __syncthreads();
   for (int i = tid; i < RB; i += nthr) {
     int m = 0;
@@ -247,74 +231,100 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
     fmask[i] = m;
   }
   __syncthreads();
-  // From here on the warps are independent.
 
-  float* stA = stage + (size_t)warp * (2 * pxw * NV);   // [pxw][NV] contributions to column dlo(x)
-  float* stB = stA + pxw * NV;                          // [pxw][NV] ... to column dlo(x) + 1
-  const int wx0 = warp * pxw, wx1 = min(wx0 + pxw, p.iW);
   float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + p.partOff) +
-                ((size_t)((size_t)n * p.nbands + band) * p.nwarps + warp) * p.pTile * NV;
+                ((size_t)n * p.nbands + band) * p.pTile * NV;
 
-  // ---- horizontal pass of one finished output row (scale s, live row k of the accumulators) ----
-  bool sawnan = false;                                       // warp-uniform: the NaN-weight slots are in use
-  auto flush = [&](int s, int k, const float (&av)[4], int dy) {
-    if (dy >= p.oH[s]) return;                               // uniform
-    {
-      float an[4] = {0.f, 0.f, 0.f, 0.f};
-      if (sawnan) {
-        const float4 t = nanw[(s * 2 + k) * nthr];
-        an[0] = t.x; an[1] = t.y; an[2] = t.z; an[3] = t.w;
-      }
-      const float2* cw = colW + s * ncols + tid * PX;
-#pragma unroll
-      for (int q = 0; q < PX; ++q) {
-        const float2 w = cw[q];
-        float a_[NV], b_[NV];
-#pragma unroll
-        for (int c = 0; c < CT; ++c) {
-          a_[c] = w.x * av[q * CT + c]; a_[CT + c] = w.x * an[q * CT + c];
-          b_[c] = w.y * av[q * CT + c]; b_[CT + c] = w.y * an[q * CT + c];
-        }
-        if constexpr (NV == 4) {
-          *reinterpret_cast<float4*>(stA + (lane * PX + q) * 4) = make_float4(a_[0], a_[1], a_[2], a_[3]);
-          *reinterpret_cast<float4*>(stB + (lane * PX + q) * 4) = make_float4(b_[0], b_[1], b_[2], b_[3]);
-        } else {
-          *reinterpret_cast<float2*>(stA + (lane * PX + q) * 2) = make_float2(a_[0], a_[1]);
-          *reinterpret_cast<float2*>(stB + (lane * PX + q) * 2) = make_float2(b_[0], b_[1]);
-        }
-      }
-    }
-    __syncwarp();
-    const int cf = wcol[(warp * MS + s) * 2], cl = wcol[(warp * MS + s) * 2 + 1];
-    const int J = p.J[s];
+  // ---- horizontal pass of one parked row (scale s, output row dy), by the whole CTA ----
+  auto hpass = [&](int s, int dy, int slot, bool withnan) {
+    const float* st = reinterpret_cast<const float*>(stage + (size_t)slot * nthr);
+    const float* nst = reinterpret_cast<const float*>(nstage);
+    const int oW = p.oW[s];
+    const int J = p.J[s], cpp = nthr / J;
     const int* cs = colS + (p.t.colS[s] - p.t.colS[0]);
-    const int jl = lane & (J - 1);
-    float* prow = part + ((size_t)p.pOff[s] + (size_t)(dy - rowD[s * RB]) * p.maxCols[s]) * NV;
-    for (int j0 = 0; cf + j0 <= cl; j0 += 32 / J) {
-      const int j = j0 + lane / J;
-      const int dx = cf + j;
-      const bool live = dx <= cl;
+    const float2* cw = colW + s * iW;
+    float* prow = part + ((size_t)p.pOff[s] + (size_t)(dy - rowD[s * RB]) * oW) * NV;
+    const int j = tid & (J - 1), c = tid / J;
+    for (int c0 = 0; c0 < oW; c0 += cpp) {
+      const int dx = c0 + c;
+      const bool live = dx < oW;
       float acc[NV];
 #pragma unroll
       for (int k = 0; k < NV; ++k) acc[k] = 0.f;
       if (live) {
-        const int c1 = cs[dx], c2 = cs[dx + 1];
-        if (dx > 0)
-          for (int xx = max(cs[dx - 1], wx0) + jl; xx < min(c1, wx1); xx += J)     // columns whose right neighbour is dx
-            add_entry<NV>(acc, stB + (xx - wx0) * NV);
-        for (int xx = max(c1, wx0) + jl; xx < min(c2, wx1); xx += J)               // columns whose left neighbour is dx
-          add_entry<NV>(acc, stA + (xx - wx0) * NV);
+        const int xa = dx > 0 ? cs[dx - 1] : 0, xm = cs[dx], xb = cs[dx + 1];
+        for (int x = xa + j; x < xb; x += J) {      // columns whose right (x < xm) or left neighbour is dx
+          const float2 w = cw[x];
+          const float wt = x < xm ? w.y : w.x;
+          if constexpr (CT == 2) {
+            const float2 a = reinterpret_cast<const float2*>(st)[x];
+            acc[0] = fmaf(wt, a.x, acc[0]); acc[1] = fmaf(wt, a.y, acc[1]);
+            if (withnan) {
+              const float2 b = reinterpret_cast<const float2*>(nst)[x];
+              acc[2] = fmaf(wt, b.x, acc[2]); acc[3] = fmaf(wt, b.y, acc[3]);
+            }
+          } else {
+            acc[0] = fmaf(wt, st[x], acc[0]);
+            if (withnan) acc[1] = fmaf(wt, nst[x], acc[1]);
+          }
+        }
       }
       for (int off = J >> 1; off >= 1; off >>= 1) {
 #pragma unroll
         for (int k = 0; k < NV; ++k) acc[k] += __shfl_xor_sync(FULL, acc[k], off);
       }
-      if (live && jl == 0) {
-        if constexpr (NV == 4) *reinterpret_cast<float4*>(prow + j * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        else *reinterpret_cast<float2*>(prow + j * 2) = make_float2(acc[0], acc[1]);
+      if (live && j == 0) {
+        if constexpr (NV == 4) *reinterpret_cast<float4*>(prow + dx * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        else *reinterpret_cast<float2*>(prow + dx * 2) = make_float2(acc[0], acc[1]);
       }
     }
-    __syncwarp();                                            // the strip may be overwritten
+  };
+
+  uint64_t nanbits = 0;       // bit 4 * i + f: float f of this thread was NaN in row i of the band
+  // NaN weight of this thread's floats towards output row dy of scale s: the running sum the walk would have kept
+  auto nan_weights = [&](int s, int dy) {
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (nanbits != 0) {
+      for (int i = 0; i < nrows; ++i) {
+        const unsigned bits = (unsigned)(nanbits >> (4 * i)) & 15u;
+        if (bits == 0) continue;
+        const int d = rowD[s * RB + i];
+        const float2 w = rowW[s * RB + i];
+        const float wt = d == dy ? w.x : (d + 1 == dy ? w.y : 0.f);
+#pragma unroll
+        for (int f = 0; f < 4; ++f) a[f] = fmaf((bits >> f) & 1u ? 1.f : 0.f, wt, a[f]);
+      }
+    }
+    return make_float4(a[0], a[1], a[2], a[3]);
+  };
+
+  // flush of the items (scale s, live row k) whose bit 2 * s + k is set in `items`; `group` picks the slots
+  auto flush = [&](unsigned items, int group, const float (&av)[MS][2][4], int i_last) {
+    int slot = group * MS;
+#pragma unroll
+    for (int s = 0; s < MS; ++s)
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        if ((items >> (2 * s + k)) & 1u)
+          stage[(size_t)(slot++) * nthr + tid] = make_float4(av[s][k][0], av[s][k][1], av[s][k][2], av[s][k][3]);
+    const bool any = __syncthreads_or(nanbits != 0);
+    slot = group * MS;
+    for (int s = 0; s < MS; ++s)
+      for (int k = 0; k < 2; ++k)
+        if ((items >> (2 * s + k)) & 1u) {
+          const int dy = rowD[s * RB + i_last] + k;
+          if (dy < p.oH[s]) {                                // uniform
+            if (!any) {
+              hpass(s, dy, slot, false);
+            } else {
+              nstage[tid] = nan_weights(s, dy);
+              __syncthreads();
+              hpass(s, dy, slot, true);
+              __syncthreads();
+            }
+          }
+          ++slot;
+        }
   };
 
   // ---- walk the rows ----
@@ -326,41 +336,39 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
 #pragma unroll
       for (int f = 0; f < 4; ++f) av[s][k][f] = 0.f;
   const float scale = p.in_scale;
+  int group = 0;
 
   for (int y0 = yb; y0 <= ye; y0 += U) {
-    if (y0 > yb) {
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-        v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(y0 + u, ye) * p.iW * CT));
-    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
+      const float4 cur = v[u];
+      if (y0 + U + u <= ye)                                // uniform: U loads stay in flight
+        v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)(y0 + U + u) * iW * CT));
       if (y0 + u <= ye) {                                  // uniform
         const int i = y0 + u - yb;
         const int m = fmask[i];
-        if (m != 0) {                                      // uniform: some scale passed the centre of its next row
+        if (m != 0) {                                      // uniform: some scales passed the centre of their next row
+          unsigned items = 0;
+#pragma unroll
+          for (int s = 0; s < MS; ++s) items |= ((m >> s) & 1) ? (1u << (2 * s)) : 0u;
+          flush(items, group, av, i - 1);
+          group ^= 1;
 #pragma unroll
           for (int s = 0; s < MS; ++s)
             if ((m >> s) & 1) {
-              flush(s, 0, av[s][0], rowD[s * RB + i - 1]);
 #pragma unroll
               for (int f = 0; f < 4; ++f) { av[s][0][f] = av[s][1][f]; av[s][1][f] = 0.f; }
-              if (sawnan) {
-                nanw[(s * 2) * nthr] = nanw[(s * 2 + 1) * nthr];
-                nanw[(s * 2 + 1) * nthr] = make_float4(0.f, 0.f, 0.f, 0.f);
-              }
             }
         }
         // flow * in_scale is a rounded fp32 product, as if the scaled tensor had been materialised (flownet_c.py:128)
-        const float x[4] = {__fmul_rn(v[u].x, scale), __fmul_rn(v[u].y, scale), __fmul_rn(v[u].z, scale),
-                            __fmul_rn(v[u].w, scale)};
+        const float x[4] = {__fmul_rn(cur.x, scale), __fmul_rn(cur.y, scale), __fmul_rn(cur.z, scale),
+                            __fmul_rn(cur.w, scale)};
         float sv[4];
-        bool anynan = false;
 #pragma unroll
         for (int f = 0; f < 4; ++f) {                      // NaN samples only count in the NaN weight (:61-65)
           const bool fin = x[f] == x[f];
           sv[f] = fin ? x[f] : 0.f;
-          anynan |= !fin;
+          if (!fin) nanbits |= 1ull << (4 * i + f);
         }
 #pragma unroll
         for (int s = 0; s < MS; ++s) {
@@ -371,31 +379,13 @@ __global__ void __launch_bounds__(512, 1) ms_band_kernel(MsParams p, const float
             av[s][1][f] = fmaf(sv[f], w.y, av[s][1][f]);
           }
         }
-        if (__any_sync(FULL, anynan)) {                    // warp-uniform and rare: NaN weights, in the shared slots
-          if (!sawnan) {
-            sawnan = true;
-            for (int e = 0; e < MS * 2; ++e) nanw[e * nthr] = make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          const float4 nn = make_float4(x[0] == x[0] ? 0.f : 1.f, x[1] == x[1] ? 0.f : 1.f, x[2] == x[2] ? 0.f : 1.f,
-                                        x[3] == x[3] ? 0.f : 1.f);
-          for (int s = 0; s < p.ns; ++s) {
-            const float2 w = rowW[s * RB + i];
-            float4 a = nanw[(s * 2) * nthr], b = nanw[(s * 2 + 1) * nthr];
-            a.x = fmaf(nn.x, w.x, a.x); a.y = fmaf(nn.y, w.x, a.y); a.z = fmaf(nn.z, w.x, a.z); a.w = fmaf(nn.w, w.x, a.w);
-            b.x = fmaf(nn.x, w.y, b.x); b.y = fmaf(nn.y, w.y, b.y); b.z = fmaf(nn.z, w.y, b.z); b.w = fmaf(nn.w, w.y, b.w);
-            nanw[(s * 2) * nthr] = a; nanw[(s * 2 + 1) * nthr] = b;
-          }
-        }
       }
     }
   }
-#pragma unroll
-  for (int s = 0; s < MS; ++s)
-    if (s < p.ns) {
-      const int cur = rowD[s * RB + nrows - 1];
-      flush(s, 0, av[s][0], cur);
-      flush(s, 1, av[s][1], cur + 1);
-    }
+  // the band's last flush parks both live rows of every scale: it uses both slot groups, so every thread must have
+  // left the previous flush's horizontal pass
+  __syncthreads();
+  flush((1u << (2 * p.ns)) - 1u, 0, av, nrows - 1);
 }
 
 // --------------------------------------------------------------------------------------------------- combine
@@ -417,21 +407,16 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
   float epe = 0.f;
   if (live) {
     const int dy = idx / oW, dx = idx - dy * oW;
-    const int2 br = reinterpret_cast<const int2*>(wsi + p.t.bandR[s])[dy];
-    const int2 wr = reinterpret_cast<const int2*>(wsi + p.t.warpR[s])[dx];
+    const int2 br = __ldg(reinterpret_cast<const int2*>(wsi + p.t.bandR[s]) + dy);
     float acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;
-    for (int b = br.x; b <= br.y; ++b) {
-      const int slot = dy - wsi[p.t.rowD[s] + b * RB];
-      for (int w = wr.x; w <= wr.y; ++w) {
-        const int j = dx - wsi[p.t.colD[s] + w * p.pxw];
-        const float* e = parts + ((((size_t)n * p.nbands + b) * p.nwarps + w) * p.pTile + p.pOff[s] +
-                                  (size_t)slot * p.maxCols[s] + j) * NV;
-        add_entry<NV>(acc, e);
-      }
+    for (int b = br.x; b <= br.y; ++b) {                     // the bands that feed this row, in band order
+      const int slot = dy - __ldg(wsi + p.t.rowD[s] + b * RB);
+      const float* e = parts + ((((size_t)n * p.nbands + b) * p.pTile + p.pOff[s] + (size_t)slot * oW + dx)) * NV;
+      add_entry<NV>(acc, e);
     }
-    const float tot = ws[p.t.totY[s] + dy] * ws[p.t.totX[s] + dx];
+    const float tot = __ldg(ws + p.t.totY[s] + dy) * __ldg(ws + p.t.totX[s] + dx);
     const size_t o = (((size_t)n * oH + dy) * oW + dx) * CT;
     float e2 = 0.f, diff[CT];
 #pragma unroll
@@ -499,8 +484,7 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   if (ns < 1 || ns > MS || N > 65535) return false;
   p.N = N; p.iH = iH; p.iW = iW; p.ns = ns;
   p.nbands = (iH + RB - 1) / RB;
-  p.nwarps = nthr / 32;
-  p.pxw = 32 * px;
+  p.nthr = nthr;
   int words = 0, pt = 0, blk = 0;
   auto take = [&](int n) { const int at = words; words += (n + 3) / 4 * 4; return at; };   // 16-byte aligned tables
   for (int s = 0; s < ns; ++s) {
@@ -512,54 +496,59 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
     // the walk never skips an output row, whatever the rounding of the centres
     if (!(p.hs[s] >= 1.5f) || !(p.ws[s] >= 1.5f)) return false;
     p.maxRows[s] = (int)((float)(RB - 1) / p.hs[s]) + 3;
-    p.maxCols[s] = (int)((float)(p.pxw - 1) / p.ws[s]) + 3;
-    int J = 1;
-    while (J < 32 && J * 2 * p.maxCols[s] <= 32) J *= 2;
+    int J = 1;   // the CTA's threads are dealt out J to an output column
+    while (J < 32 && J * 2 * oW <= nthr) J *= 2;
     p.J[s] = J;
     p.pOff[s] = pt;
-    pt += p.maxRows[s] * p.maxCols[s];
+    pt += p.maxRows[s] * oW;
     p.blkOff[s] = blk;
     blk += (oH * oW + CB - 1) / CB;
   }
   for (int s = ns; s < MS; ++s) {   // unused scales: harmless values (their weights are zero, they are never flushed)
-    p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.maxRows[s] = p.maxCols[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
+    p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.maxRows[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
   }
   for (int s = ns; s <= MS; ++s) p.blkOff[s] = blk;
   p.pTile = pt;
   // table area; the colS tables are packed back to back and followed by totX[0] (the band kernel copies them as one run)
   for (int s = 0; s < ns; ++s) { p.t.rowW[s] = take(2 * iH); p.t.rowD[s] = take(iH); }
-  for (int s = 0; s < ns; ++s) { p.t.colW[s] = take(2 * iW); p.t.colD[s] = take(iW); }
+  for (int s = 0; s < ns; ++s) p.t.colW[s] = take(2 * iW);
   for (int s = 0; s < ns; ++s) { p.t.colS[s] = words; words += p.oW[s] + 1; }
   words = (words + 3) / 4 * 4;
   for (int s = 0; s < ns; ++s) p.t.totX[s] = take(p.oW[s]);
   for (int s = 0; s < ns; ++s) p.t.totY[s] = take(p.oH[s]);
-  for (int s = 0; s < ns; ++s) { p.t.bandR[s] = take(2 * p.oH[s]); p.t.warpR[s] = take(2 * p.oW[s]); }
-  for (int s = ns; s < MS; ++s) {
-    p.t.rowW[s] = p.t.rowD[s] = p.t.colW[s] = p.t.colD[s] = p.t.colS[s] = p.t.totX[s] = p.t.totY[s] = p.t.bandR[s] =
-        p.t.warpR[s] = 0;
-  }
+  for (int s = 0; s < ns; ++s) p.t.bandR[s] = take(2 * p.oH[s]);
+  for (int s = ns; s < MS; ++s)
+    p.t.rowW[s] = p.t.rowD[s] = p.t.colW[s] = p.t.colS[s] = p.t.totX[s] = p.t.totY[s] = p.t.bandR[s] = 0;
   p.t.words = words;
   const long long nblocks = (long long)N * blk;
   if (nblocks > 0x7fffffffLL) return false;
   p.ctrlOff = align_up((size_t)words * 4, 256);
   p.partOff = align_up(p.ctrlOff + 16 + (size_t)nblocks * 4, 256);
-  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.nwarps * p.pTile * (2 * C) * sizeof(float);
-  *band_smem = band_smem_layout(p.nwarps, px, 2 * C, p.t.totX[0] - p.t.colS[0]).total;
-  return *band_smem <= 160 * 1024;
+  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.pTile * (2 * C) * sizeof(float);
+  *band_smem = band_smem_layout(nthr, iW, p.t.totX[0] - p.t.colS[0]).total;
+  return *band_smem <= 200 * 1024;
 }
 
 template <int CT>
 int ms_launch(const MsParams& p, size_t band_smem, const float* in, void* ws, cudaStream_t st) {
   static PerDeviceOnce once;   // per template instantiation; function attributes are per device
   const cudaError_t attr_err = per_device_once(once, [] {
-    return cudaFuncSetAttribute(ms_band_kernel<CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(ms_band_kernel<CT, 256, DS_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         200 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(ms_band_kernel<CT, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    return e;
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
   float* w = static_cast<float*>(ws);
   ms_tables_kernel<<<dim3(TBX, (unsigned)p.ns), 256, 0, st>>>(p, w);
   int rc = after_launch();
   if (rc != FN2_OK) return rc;
-  ms_band_kernel<CT><<<dim3((unsigned)p.nbands, (unsigned)p.N), p.nwarps * 32, band_smem, st>>>(p, in, w);
+  const dim3 grid((unsigned)p.nbands, (unsigned)p.N);
+  if (p.nthr <= 256)
+    ms_band_kernel<CT, 256, DS_MINB><<<grid, p.nthr, band_smem, st>>>(p, in, w);
+  else
+    ms_band_kernel<CT, 512, 1><<<grid, p.nthr, band_smem, st>>>(p, in, w);
   rc = after_launch();
   if (rc != FN2_OK) return rc;
   ms_combine_kernel<CT><<<(unsigned)(p.N * p.blkOff[p.ns]), CB, 0, st>>>(p, w);

@@ -75,3 +75,22 @@ def test_cuda_reproduces_reference_warp_and_downsample():
         if key.startswith("out_"):
             size = [int(v) for v in key.split("_")[1:]]
             assert_close(fn2.downsample(x, size).cpu().numpy(), z[key], rel=1e-5, abs_=5e-6, what=key)
+
+
+def test_both_oracles_agree_on_the_reference_sample_pair():
+    """tests/golden/sample0.npz = the reference's data/samples pair 0 (made by tests/golden/make_fixtures.py): the C
+    restatement and the independent float64 numpy restatement give the same warp, gradients and downsampled flow on
+    real data (smooth flows, displacements down to -108.9 px, pixel values 0..255)."""
+    z = np.load(os.path.join(GOLD, "sample0.npz"))
+    assert z["image"].shape == (384, 512, 3) and z["flow"].shape == (384, 512, 2)
+    assert float(z["flow"].min()) == -108.90625
+    image = z["image"].astype(np.float32)[None, 100:228, 200:392]
+    flow = np.ascontiguousarray(z["flow"][None, 100:228, 200:392])
+    assert_close(o.c_flow_warp(image, flow), o.np_flow_warp(image, flow), rel=1e-5, abs_=1e-4, what="warp")
+    g = np.random.default_rng(0).standard_normal(image.shape).astype(np.float32)
+    ci, cf = o.c_flow_warp_grad(image, flow, g)
+    ni, nf = o.np_flow_warp_grad(image, flow, g)
+    assert_close(ci, ni, rel=1e-5, abs_=2e-5, what="image_grad")
+    assert_close(cf, nf, rel=1e-5, abs_=2e-3, what="flow_grad")
+    for size in [(6, 8), (24, 32)]:
+        assert_close(o.c_downsample(flow, size), o.np_downsample(flow, size), rel=1e-5, abs_=5e-6, what=str(size))
