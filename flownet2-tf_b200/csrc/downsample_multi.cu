@@ -9,25 +9,29 @@
 //
 // Three launches, no atomics on data, a fixed summation order that does not depend on the batch size:
 //   0. ms_tables_kernel   -- the weight tables, which depend only on the shapes: per (scale, input row) the output row
-//      dlo below it and its two vertical weights, the same per input column, the column ranges of every output column,
-//      the total weights, and which tiles feed which output.  One thread (or warp) per entry; the IEEE divisions of the
-//      reference's formula are done once per launch here, not once per CTA.
-//   1. ms_band_kernel     -- grid (row bands of 16 input rows) x (images): short CTAs, many waves.  A thread owns 4
-//      adjacent floats of a row (16-byte loads, 4 rows in flight) and reads each exactly once.  The weight is separable,
-//      w = wx(x) * wy(y), and an input row feeds at most two output rows of every scale (the last centre at or above
-//      it, and the next one), so the thread keeps, per scale, the vertical value sums of those two live output rows in
-//      registers (the NaN-weight sums live in thread-private shared-memory slots that are only touched once a warp
-//      has met a NaN: none of that work is done for NaN-free input).  When the walk passes the centre of the next output row of a scale (a block-uniform
-//      branch) the finished row is reduced horizontally BY EACH WARP ON ITS OWN: the lanes park their x-weighted column
-//      sums in the warp's private shared-memory strip, and small lane groups add up the strip's share of every output
-//      column it touches in a fixed order.  No block barrier, no cluster: warps never wait for each other.  The warp's
-//      partial rows go to the caller's workspace (they stay in L2).
-//   2. ms_combine_kernel  -- one thread per output pixel adds the partials of the (band, warp) tiles that feed it, in
-//      tile order, applies the NaN rule (:72-76) and writes the downsampled value; when predictions are given it also
-//      forms the end-point error sqrt(sum_c (pred - down)^2), the unit residual (pred - down) / epe that the loss
-//      gradient needs, and the per-scale sums (block tree, then one ordered pass by the last block to finish).
-// NaN samples: the reference keeps accum_weight (non-NaN samples) and accum_nan; here the NaN weight is accumulated
-// itself (exactly zero when there is no NaN) and accum_weight = total weight - accum_nan, the total being a table.
+//      dlo below it and its two vertical weights, the same per input column, the first input column of every output
+//      column's interval, the total weights, and which bands feed which output row.  One thread (or warp) per entry;
+//      the IEEE divisions of the reference's formula are done once per launch here, not once per CTA.
+//   1. ms_band_kernel     -- grid (bands of 16 input rows) x (images).  The band (64 KB for a 512 x 2 flow) is copied
+//      into shared memory by the bulk-copy engine in one go; nothing else ever reads the input.  The weight is
+//      separable, w = wx(x) * wy(y).  HORIZONTAL FIRST: the input columns between two output-column centres of a scale
+//      form an interval whose pixels feed exactly those two output columns; J lanes share an interval, each owning a
+//      16-byte-aligned run of at most 10 pixels whose x-weights (towards the left centre, A, and the right one, B) sit
+//      in registers for the whole band.  Per input row a thread reads its run once (<= 5 16-byte loads, conflict
+//      free), forms the two x-weighted sums, and adds them, y-weighted, to the vertical sums of the (at most) two
+//      live output rows of its scale -- all in registers, no barrier, no shuffle.  When the walk passes the centre
+//      of the next output row of the thread's scale (warp-uniform: a warp serves one scale) the J lanes join their
+//      sums with a fixed shuffle tree and one lane stores the partial (A and B part of the interval) to the caller's
+//      workspace (it stays in L2).  Every pixel is read from shared memory once per scale.
+//   2. ms_combine_kernel  -- one thread per output pixel adds, band by band, the A part of its own interval and the B
+//      part of the interval to its left, applies the NaN rule (:72-76) and writes the downsampled value; when
+//      predictions are given it also forms the end-point error sqrt(sum_c (pred - down)^2), the unit residual
+//      (pred - down) / epe that the loss gradient needs, and the per-scale sums (block tree, then one ordered pass by
+//      the last block to finish).
+// NaN samples: the fast path multiplies and adds blindly; a NaN (or an infinity meeting a zero weight) turns the row's
+// sums into NaN, which sends THAT thread and row through the careful path (sample != sample -> counted in the NaN
+// weight instead, :61-65) and marks the row; the NaN weights are rebuilt from the marked rows (still in shared memory)
+// when an output row is stored.  accum_weight = total weight - accum_nan, the total being a table.
 #include <cstdlib>
 #include "fn2_common.cuh"
 #include "fn2_downsample.cuh"
@@ -38,13 +42,9 @@ namespace {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MS = 5;     // scales per launch (the reference's losses use five, flownet_c.py:135-160)
 constexpr int RB = 16;    // input rows per band: fixed, so the summation order never depends on the batch size
-constexpr int U = 4;      // rows in flight per thread
 constexpr int CB = 256;   // threads of the combine kernel
-constexpr int NSLOT = 2 * MS;   // staged rows: two groups of MS used alternately, all of them by the band's last flush
-#ifndef DS_MINB
-#define DS_MINB 2
-#endif
-static_assert(RB * 4 <= 64, "one NaN bit per (row, float) of a thread in a 64-bit word");
+constexpr int MAXBANDS = 1024;   // bands per image the combine kernel keeps a table for (iH <= 16384)
+static_assert(RB <= 32, "one marked-row bit per row of the band");
 
 // Offsets (4-byte words) of the per-scale tables inside the workspace.
 struct MsTables {
@@ -63,7 +63,8 @@ struct MsParams {
   int nbands, nthr;               // bands per image, threads of a band CTA (a multiple of 32)
   int oH[MS], oW[MS];
   int maxRows[MS];                // output rows a band can touch
-  int J[MS];                      // lanes that share one output column in the horizontal pass (a power of two <= 32)
+  int J[MS], L[MS];               // lanes per interval (a power of two <= 32), pixels per lane (a multiple of 4 / C)
+  int tOff[MS + 1];               // first thread of scale s in a band CTA (multiples of 32)
   int pOff[MS], pTile;            // partial entries: offset of scale s inside a band's tile, entries per tile
   int blkOff[MS + 1];             // combine kernel: first block of scale s within an image
   float hs[MS], ws[MS];
@@ -76,24 +77,24 @@ struct MsParams {
   size_t ctrlOff, partOff;        // byte offsets in the workspace: control block (ticket + block sums), partials
 };
 
-// Shared-memory layout of the band kernel (bytes, every area 16-byte aligned); used by the host for the launch size.
+// Shared-memory layout of the band kernel (bytes); used by the host for the launch size.
 struct BandSmem {
-  size_t rowW, rowD, fmask, colS, colW, stage, nstage, total;
+  size_t band, rowW, rowD, fmask, bar, total;
 };
 __host__ __device__ inline size_t up16(size_t v) { return (v + 15) & ~(size_t)15; }
-__host__ __device__ inline BandSmem band_smem_layout(int nthr, int iW, int cswords) {
+__host__ __device__ inline BandSmem band_smem_layout(int rowfloats) {
   BandSmem L;
   size_t o = 0;
+  L.band = o; o = up16(o + (size_t)RB * rowfloats * 4);
   L.rowW = o; o = up16(o + (size_t)MS * RB * 8);
   L.rowD = o; o = up16(o + (size_t)MS * RB * 4);
   L.fmask = o; o = up16(o + (size_t)RB * 4);
-  L.colS = o; o = up16(o + (size_t)cswords * 4);
-  L.colW = o; o = up16(o + (size_t)MS * iW * 8);
-  L.stage = o; o = up16(o + (size_t)NSLOT * nthr * 16);
-  L.nstage = o; o = up16(o + (size_t)nthr * 16);
+  L.bar = o; o = up16(o + 8);
   L.total = o;
   return L;
 }
+
+__device__ __forceinline__ uint32_t ms_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ---------------------------------------------------------------------------------------------------- tables
 // grid (TBX, ns): blockIdx.y = scale; the entries of a scale are independent, each on its own thread (rows, columns,
@@ -164,228 +165,213 @@ __device__ __forceinline__ void add_entry(float (&acc)[NV], const float* e) {
 }
 
 // ------------------------------------------------------------------------------------------------- band walk
-// grid (bands of RB input rows) x (images); CT channels; a thread owns the 4 floats (PX = 4 / CT adjacent pixels) of one
-// 16-byte column slot and walks the band's rows downwards, U rows in flight, reading every input byte exactly once.
-// The weight is separable, w = wx(x) * wy(y), and an input row feeds at most two output rows of every scale (the last
-// centre at or above it, and the next one): per scale the thread keeps the VERTICAL sums of those two live output rows
-// of its 4 floats in registers (2 FMAs per float, scale and row).  When the walk passes the centre of the next output
-// row of some scales (a block-uniform event, fmask) the finished rows are parked in shared memory -- one 16-byte store
-// per thread and row --, ONE block barrier follows, and the whole CTA sums each parked row horizontally: J lanes share
-// an output column, each adds its share of the column's window in a fixed order (x-weights from a shared copy of the
-// table), a fixed shuffle tree joins the J partial sums, and the band's partial output row goes to the caller's
-// workspace (it stays in L2).  Parked rows alternate between two groups of slots, so no second barrier is needed.
-// NaN samples are rare: the walk only records WHERE they were (one bit per row and float); the barrier of a flush also
-// tells whether any thread of the CTA has met one (__syncthreads_or), and only then the NaN weights of the parked rows
-// are rebuilt from the bits (same additions, same order as a running sum) and summed like the values.
-template <int CT, int MAXT, int MINB>
-__global__ void __launch_bounds__(MAXT, MINB) ms_band_kernel(MsParams p, const float* __restrict__ in,
-                                                             float* __restrict__ ws) {
-  constexpr int PX = 4 / CT;
-  constexpr int NV = 2 * CT;                    // per output pixel: value and NaN-weight sums per channel
-  extern __shared__ __align__(16) uint8_t sm[];
-  const int tid = threadIdx.x, nthr = blockDim.x;
-  const int lane = tid & 31;
+// CT channels; PXV = 4 / CT pixels per 16-byte vector; a thread owns at most NVEC vectors (P pixels) of every row.
+// Partial entry of (band, scale, output row, interval dx): [A values x CT, A NaN weights x CT, B values, B NaN weights].
+template <int CT, bool SCALED>
+__global__ void __launch_bounds__(1024, 1) ms_band_kernel(MsParams p, const float* __restrict__ in,
+                                                          float* __restrict__ ws) {
+  constexpr int PXV = 4 / CT;
+  constexpr int NVEC = CT == 2 ? 5 : 3;
+  constexpr int P = NVEC * PXV;
+  constexpr int NE = 4 * CT;
+  extern __shared__ __align__(128) uint8_t sm[];
+  const int tid = threadIdx.x, lane = tid & 31;
   const int band = blockIdx.x, n = blockIdx.y;
   const int yb = band * RB, ye = min(p.iH - 1, yb + RB - 1);
   const int nrows = ye - yb + 1;
-  const int iW = p.iW;
+  const int iW = p.iW, rowf = iW * CT;
   const int* wsi = reinterpret_cast<const int*>(ws);
+  const BandSmem Ls = band_smem_layout(rowf);
+  const float* bandbuf = reinterpret_cast<const float*>(sm + Ls.band);
+  float2* rowW = reinterpret_cast<float2*>(sm + Ls.rowW);     // [MS][RB]
+  int* rowD = reinterpret_cast<int*>(sm + Ls.rowD);           // [MS][RB]
+  int* fmask = reinterpret_cast<int*>(sm + Ls.fmask);         // [RB] bit s: scale s finishes an output row before row i
+  const uint32_t bar = ms_smem_u32(sm + Ls.bar);
 
-  // the colS tables are packed back to back in the workspace and followed by totX[0]
-  const int cswords = p.t.totX[0] - p.t.colS[0];
-  const BandSmem L = band_smem_layout(nthr, iW, cswords);
-  float2* rowW = reinterpret_cast<float2*>(sm + L.rowW);     // [MS][RB]
-  int* rowD = reinterpret_cast<int*>(sm + L.rowD);           // [MS][RB]
-  int* fmask = reinterpret_cast<int*>(sm + L.fmask);         // [RB] bit s: scale s finishes an output row before row i
-  int* colS = reinterpret_cast<int*>(sm + L.colS);           // per scale [oW + 1], packed
-  float2* colW = reinterpret_cast<float2*>(sm + L.colW);     // [MS][iW]
-  float4* stage = reinterpret_cast<float4*>(sm + L.stage);   // [NSLOT][nthr]: parked rows of vertical sums
-  float4* nstage = reinterpret_cast<float4*>(sm + L.nstage); // [nthr]: NaN weights of one parked row (rare path)
+  // ---- the band, by the bulk-copy engine: one request per 16 rows at most, one barrier ----
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const uint32_t bytes = (uint32_t)nrows * (uint32_t)rowf * 4u;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    const float* src = in + ((size_t)n * p.iH + yb) * rowf;
+    uint32_t done = 0;
+    while (done < bytes) {
+      const uint32_t chunk = min(bytes - done, 32768u);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(ms_smem_u32(sm + Ls.band) + done), "l"(reinterpret_cast<const char*>(src) + done), "r"(chunk),
+                     "r"(bar) : "memory");
+      done += chunk;
+    }
+  }
 
-  // the first rows are requested before anything else so that their latency overlaps the table copy
-  const int x0 = tid * PX;
-  const float* col = in + ((size_t)n * p.iH * iW + (size_t)min(x0, iW - PX)) * CT;
-  float4 v[U];
+  // ---- which interval, which run ----
+  int s = 0;
+  while (s + 1 < p.ns && tid >= p.tOff[s + 1]) ++s;           // warp-uniform: tOff are multiples of 32
+  const int local = tid - p.tOff[s];
+  const int J = p.J[s], Lr = p.L[s];
+  const int dx = local / J, j = local & (J - 1);
+  const int oW = p.oW[s];
+  const bool active = dx < oW;
+  float wA[P], wB[P];
+  int vec0 = 0, nvec = 0;
+  {
+    const int* cs = wsi + p.t.colS[s];
+    const int c0 = active ? __ldg(cs + dx) : 0, c1 = active ? __ldg(cs + dx + 1) : 0;
+    const int rr = (c0 & ~(PXV - 1)) + j * Lr;               // this lane's share of the interval: [rr, rr + Lr)
+    const int lo = max(c0, rr), hi = min(c1, rr + Lr);
+    const int r0 = lo & ~(PXV - 1);                           // the 16-byte vector that holds its first column
+    const float2* cw = reinterpret_cast<const float2*>(ws + p.t.colW[s]);
 #pragma unroll
-  for (int u = 0; u < U; ++u) v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)min(yb + u, ye) * iW * CT));
+    for (int k = 0; k < P; ++k) {
+      const int px = r0 + k;
+      const bool in_run = active && px >= lo && px < hi;
+      const float2 w = in_run ? __ldg(cw + px) : make_float2(0.f, 0.f);
+      wA[k] = w.x; wB[k] = w.y;
+    }
+    vec0 = r0 / PXV;
+    nvec = (active && hi > lo) ? (hi - r0 + PXV - 1) / PXV : 0;   // <= Lr / PXV: rr is vector aligned
+  }
 
-  // ---- this band's slice of the row tables, the column tables ----
-  for (int idx = tid; idx < MS * RB; idx += nthr) {
-    const int s = idx / RB, i = idx - s * RB;
+  // ---- this band's slice of the row tables ----
+  for (int idx = tid; idx < MS * RB; idx += blockDim.x) {
+    const int sc = idx / RB, i = idx - sc * RB;
     float2 w = make_float2(0.f, 0.f);
     int d = 0;
-    if (s < p.ns && i < nrows) {
-      w = __ldg(reinterpret_cast<const float2*>(ws + p.t.rowW[s]) + yb + i);
-      d = __ldg(wsi + p.t.rowD[s] + yb + i);
+    if (sc < p.ns && i < nrows) {
+      w = __ldg(reinterpret_cast<const float2*>(ws + p.t.rowW[sc]) + yb + i);
+      d = __ldg(wsi + p.t.rowD[sc] + yb + i);
     }
     rowW[idx] = w; rowD[idx] = d;
   }
-  for (int s = 0; s < p.ns; ++s)
-    for (int x = tid; x < iW; x += nthr) colW[s * iW + x] = __ldg(reinterpret_cast<const float2*>(ws + p.t.colW[s]) + x);
-  for (int i = tid; i < cswords; i += nthr) colS[i] = __ldg(wsi + p.t.colS[0] + i);
-  __syncthreads();
-  for (int i = tid; i < RB; i += nthr) {
+  __syncthreads();                                            // also: the barrier is initialised before anyone polls it
+  for (int i = tid; i < RB; i += blockDim.x) {
     int m = 0;
     if (i > 0 && i < nrows)
-      for (int s = 0; s < p.ns; ++s) m |= (rowD[s * RB + i] != rowD[s * RB + i - 1]) ? (1 << s) : 0;
+      for (int sc = 0; sc < p.ns; ++sc) m |= (rowD[sc * RB + i] != rowD[sc * RB + i - 1]) ? (1 << sc) : 0;
     fmask[i] = m;
   }
   __syncthreads();
+  {
+    uint32_t ok = 0;
+    while (!ok) {
+      asm volatile("{\n.reg .pred q;\nmbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0;\nselp.u32 %0, 1, 0, q;\n}"
+                   : "=r"(ok) : "r"(bar) : "memory");
+    }
+  }
 
+  const float scale = p.in_scale;
   float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + p.partOff) +
-                ((size_t)n * p.nbands + band) * p.pTile * NV;
+                (((size_t)n * p.nbands + band) * p.pTile + p.pOff[s]) * NE;
+  const int d_first = rowD[s * RB];
+  const float4* vbase = reinterpret_cast<const float4*>(bandbuf) + vec0;
+  const int rowv = rowf / 4;                                  // 16-byte vectors per row
 
-  // ---- horizontal pass of one parked row (scale s, output row dy), by the whole CTA ----
-  auto hpass = [&](int s, int dy, int slot, bool withnan) {
-    const float* st = reinterpret_cast<const float*>(stage + (size_t)slot * nthr);
-    const float* nst = reinterpret_cast<const float*>(nstage);
-    const int oW = p.oW[s];
-    const int J = p.J[s], cpp = nthr / J;
-    const int* cs = colS + (p.t.colS[s] - p.t.colS[0]);
-    const float2* cw = colW + s * iW;
-    float* prow = part + ((size_t)p.pOff[s] + (size_t)(dy - rowD[s * RB]) * oW) * NV;
-    const int j = tid & (J - 1), c = tid / J;
-    for (int c0 = 0; c0 < oW; c0 += cpp) {
-      const int dx = c0 + c;
-      const bool live = dx < oW;
-      float acc[NV];
+  // x-weighted sums of one row, careful path: NaN samples are left out of the values and counted in the NaN weights
+  auto careful_row = [&](int i, float (&hA)[CT], float (&hB)[CT], float (&nA)[CT], float (&nB)[CT]) {
 #pragma unroll
-      for (int k = 0; k < NV; ++k) acc[k] = 0.f;
-      if (live) {
-        const int xa = dx > 0 ? cs[dx - 1] : 0, xm = cs[dx], xb = cs[dx + 1];
-        for (int x = xa + j; x < xb; x += J) {      // columns whose right (x < xm) or left neighbour is dx
-          const float2 w = cw[x];
-          const float wt = x < xm ? w.y : w.x;
-          if constexpr (CT == 2) {
-            const float2 a = reinterpret_cast<const float2*>(st)[x];
-            acc[0] = fmaf(wt, a.x, acc[0]); acc[1] = fmaf(wt, a.y, acc[1]);
-            if (withnan) {
-              const float2 b = reinterpret_cast<const float2*>(nst)[x];
-              acc[2] = fmaf(wt, b.x, acc[2]); acc[3] = fmaf(wt, b.y, acc[3]);
-            }
-          } else {
-            acc[0] = fmaf(wt, st[x], acc[0]);
-            if (withnan) acc[1] = fmaf(wt, nst[x], acc[1]);
+    for (int c = 0; c < CT; ++c) hA[c] = hB[c] = nA[c] = nB[c] = 0.f;
+#pragma unroll
+    for (int k = 0; k < NVEC; ++k) {
+      if (k < nvec) {
+        const float4 v = vbase[(size_t)i * rowv + k];
+        const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < PXV; ++q) {
+          const float a = wA[k * PXV + q], b = wB[k * PXV + q];
+          if (a == 0.f && b == 0.f) continue;                 // outside the run (or beyond every centre): not a sample
+#pragma unroll
+          for (int c = 0; c < CT; ++c) {
+            const float x = SCALED ? __fmul_rn(e[q * CT + c], scale) : e[q * CT + c];
+            if (x == x) { hA[c] = fmaf(a, x, hA[c]); hB[c] = fmaf(b, x, hB[c]); }
+            else { nA[c] += a; nB[c] += b; }
           }
         }
-      }
-      for (int off = J >> 1; off >= 1; off >>= 1) {
-#pragma unroll
-        for (int k = 0; k < NV; ++k) acc[k] += __shfl_xor_sync(FULL, acc[k], off);
-      }
-      if (live && j == 0) {
-        if constexpr (NV == 4) *reinterpret_cast<float4*>(prow + dx * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        else *reinterpret_cast<float2*>(prow + dx * 2) = make_float2(acc[0], acc[1]);
       }
     }
   };
 
-  uint64_t nanbits = 0;       // bit 4 * i + f: float f of this thread was NaN in row i of the band
-  // NaN weight of this thread's floats towards output row dy of scale s: the running sum the walk would have kept
-  auto nan_weights = [&](int s, int dy) {
-    float a[4] = {0.f, 0.f, 0.f, 0.f};
-    if (nanbits != 0) {
+  float accA[2][CT], accB[2][CT];
+#pragma unroll
+  for (int k = 0; k < 2; ++k)
+#pragma unroll
+    for (int c = 0; c < CT; ++c) accA[k][c] = accB[k][c] = 0.f;
+  unsigned marked = 0;                                        // bit i: row i of the band took the careful path here
+
+  // stores output row dy (live row k of the accumulators) of this thread's interval
+  auto flush = [&](int k, int dy) {
+    if (dy >= p.oH[s]) return;                                // warp-uniform
+    float v[NE];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) { v[c] = accA[k][c]; v[CT + c] = 0.f; v[2 * CT + c] = accB[k][c]; v[3 * CT + c] = 0.f; }
+    if (__any_sync(FULL, marked != 0)) {                      // rare: rebuild the NaN weights from the marked rows
       for (int i = 0; i < nrows; ++i) {
-        const unsigned bits = (unsigned)(nanbits >> (4 * i)) & 15u;
-        if (bits == 0) continue;
+        if (!((marked >> i) & 1u)) continue;
         const int d = rowD[s * RB + i];
         const float2 w = rowW[s * RB + i];
-        const float wt = d == dy ? w.x : (d + 1 == dy ? w.y : 0.f);
+        const float wy = d == dy ? w.x : (d + 1 == dy ? w.y : 0.f);
+        if (wy == 0.f) continue;
+        float hA[CT], hB[CT], nA[CT], nB[CT];
+        careful_row(i, hA, hB, nA, nB);
 #pragma unroll
-        for (int f = 0; f < 4; ++f) a[f] = fmaf((bits >> f) & 1u ? 1.f : 0.f, wt, a[f]);
+        for (int c = 0; c < CT; ++c) { v[CT + c] = fmaf(wy, nA[c], v[CT + c]); v[3 * CT + c] = fmaf(wy, nB[c], v[3 * CT + c]); }
       }
     }
-    return make_float4(a[0], a[1], a[2], a[3]);
-  };
-
-  // flush of the items (scale s, live row k) whose bit 2 * s + k is set in `items`; `group` picks the slots
-  auto flush = [&](unsigned items, int group, const float (&av)[MS][2][4], int i_last) {
-    int slot = group * MS;
+    for (int off = J >> 1; off >= 1; off >>= 1) {             // the J lanes of an interval, a fixed tree
 #pragma unroll
-    for (int s = 0; s < MS; ++s)
-#pragma unroll
-      for (int k = 0; k < 2; ++k)
-        if ((items >> (2 * s + k)) & 1u)
-          stage[(size_t)(slot++) * nthr + tid] = make_float4(av[s][k][0], av[s][k][1], av[s][k][2], av[s][k][3]);
-    const bool any = __syncthreads_or(nanbits != 0);
-    slot = group * MS;
-    for (int s = 0; s < MS; ++s)
-      for (int k = 0; k < 2; ++k)
-        if ((items >> (2 * s + k)) & 1u) {
-          const int dy = rowD[s * RB + i_last] + k;
-          if (dy < p.oH[s]) {                                // uniform
-            if (!any) {
-              hpass(s, dy, slot, false);
-            } else {
-              nstage[tid] = nan_weights(s, dy);
-              __syncthreads();
-              hpass(s, dy, slot, true);
-              __syncthreads();
-            }
-          }
-          ++slot;
-        }
+      for (int e = 0; e < NE; ++e) v[e] += __shfl_xor_sync(FULL, v[e], off);
+    }
+    if (active && j == 0) {
+      float* e = part + ((size_t)(dy - d_first) * oW + dx) * NE;
+      *reinterpret_cast<float4*>(e) = make_float4(v[0], v[1], v[2], v[3]);
+      if constexpr (NE == 8) *reinterpret_cast<float4*>(e + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    }
   };
 
   // ---- walk the rows ----
-  float av[MS][2][4];
+  for (int i = 0; i < nrows; ++i) {
+    if ((fmask[i] >> s) & 1) {                                // warp-uniform: this scale passed the centre of its next row
+      flush(0, rowD[s * RB + i - 1]);
 #pragma unroll
-  for (int s = 0; s < MS; ++s)
+      for (int c = 0; c < CT; ++c) { accA[0][c] = accA[1][c]; accA[1][c] = 0.f; accB[0][c] = accB[1][c]; accB[1][c] = 0.f; }
+    }
+    float hA[CT], hB[CT];
 #pragma unroll
-    for (int k = 0; k < 2; ++k)
+    for (int c = 0; c < CT; ++c) hA[c] = hB[c] = 0.f;
 #pragma unroll
-      for (int f = 0; f < 4; ++f) av[s][k][f] = 0.f;
-  const float scale = p.in_scale;
-  int group = 0;
-
-  for (int y0 = yb; y0 <= ye; y0 += U) {
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const float4 cur = v[u];
-      if (y0 + U + u <= ye)                                // uniform: U loads stay in flight
-        v[u] = __ldg(reinterpret_cast<const float4*>(col + (size_t)(y0 + U + u) * iW * CT));
-      if (y0 + u <= ye) {                                  // uniform
-        const int i = y0 + u - yb;
-        const int m = fmask[i];
-        if (m != 0) {                                      // uniform: some scales passed the centre of their next row
-          unsigned items = 0;
-#pragma unroll
-          for (int s = 0; s < MS; ++s) items |= ((m >> s) & 1) ? (1u << (2 * s)) : 0u;
-          flush(items, group, av, i - 1);
-          group ^= 1;
-#pragma unroll
-          for (int s = 0; s < MS; ++s)
-            if ((m >> s) & 1) {
-#pragma unroll
-              for (int f = 0; f < 4; ++f) { av[s][0][f] = av[s][1][f]; av[s][1][f] = 0.f; }
-            }
-        }
+    for (int k = 0; k < NVEC; ++k) {
+      if (k < nvec) {
+        const float4 v = vbase[(size_t)i * rowv + k];
         // flow * in_scale is a rounded fp32 product, as if the scaled tensor had been materialised (flownet_c.py:128)
-        const float x[4] = {__fmul_rn(cur.x, scale), __fmul_rn(cur.y, scale), __fmul_rn(cur.z, scale),
-                            __fmul_rn(cur.w, scale)};
-        float sv[4];
+        const float e[4] = {SCALED ? __fmul_rn(v.x, scale) : v.x, SCALED ? __fmul_rn(v.y, scale) : v.y,
+                            SCALED ? __fmul_rn(v.z, scale) : v.z, SCALED ? __fmul_rn(v.w, scale) : v.w};
 #pragma unroll
-        for (int f = 0; f < 4; ++f) {                      // NaN samples only count in the NaN weight (:61-65)
-          const bool fin = x[f] == x[f];
-          sv[f] = fin ? x[f] : 0.f;
-          if (!fin) nanbits |= 1ull << (4 * i + f);
-        }
+        for (int q = 0; q < PXV; ++q)
 #pragma unroll
-        for (int s = 0; s < MS; ++s) {
-          const float2 w = rowW[s * RB + i];
-#pragma unroll
-          for (int f = 0; f < 4; ++f) {
-            av[s][0][f] = fmaf(sv[f], w.x, av[s][0][f]);
-            av[s][1][f] = fmaf(sv[f], w.y, av[s][1][f]);
+          for (int c = 0; c < CT; ++c) {
+            hA[c] = fmaf(wA[k * PXV + q], e[q * CT + c], hA[c]);
+            hB[c] = fmaf(wB[k * PXV + q], e[q * CT + c], hB[c]);
           }
-        }
       }
     }
+    bool bad = false;
+#pragma unroll
+    for (int c = 0; c < CT; ++c) bad |= !(hA[c] == hA[c]) || !(hB[c] == hB[c]);
+    if (bad) {                                                // a NaN sample, or an infinity next to a zero weight
+      float nA[CT], nB[CT];
+      careful_row(i, hA, hB, nA, nB);
+      marked |= 1u << i;
+    }
+    const float2 wy = rowW[s * RB + i];
+#pragma unroll
+    for (int c = 0; c < CT; ++c) {
+      accA[0][c] = fmaf(wy.x, hA[c], accA[0][c]); accA[1][c] = fmaf(wy.y, hA[c], accA[1][c]);
+      accB[0][c] = fmaf(wy.x, hB[c], accB[0][c]); accB[1][c] = fmaf(wy.y, hB[c], accB[1][c]);
+    }
   }
-  // the band's last flush parks both live rows of every scale: it uses both slot groups, so every thread must have
-  // left the previous flush's horizontal pass
-  __syncthreads();
-  flush((1u << (2 * p.ns)) - 1u, 0, av, nrows - 1);
+  const int cur = rowD[s * RB + nrows - 1];
+  flush(0, cur);
+  flush(1, cur + 1);
 }
 
 // --------------------------------------------------------------------------------------------------- combine
@@ -394,6 +380,7 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
   constexpr int NV = 2 * CT;
   __shared__ float red[CB / 32];
   __shared__ bool lastBlock;
+  __shared__ int dfirst[MAXBANDS];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bpi = p.blkOff[p.ns];
   const int n = blockIdx.x / bpi, rb = blockIdx.x - n * bpi;
@@ -404,6 +391,9 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
   const bool live = idx < oH * oW;
   const int* wsi = reinterpret_cast<const int*>(ws);
   const float* parts = reinterpret_cast<const float*>(reinterpret_cast<const char*>(ws) + p.partOff);
+  // first output row each band touches (the row its partial slots count from)
+  for (int b = tid; b < p.nbands; b += CB) dfirst[b] = __ldg(wsi + p.t.rowD[s] + b * RB);
+  __syncthreads();
   float epe = 0.f;
   if (live) {
     const int dy = idx / oW, dx = idx - dy * oW;
@@ -411,10 +401,13 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
     float acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;
+    const float* base = parts + ((size_t)n * p.nbands * p.pTile + p.pOff[s] + dx) * (2 * NV);
+    const size_t bstride = (size_t)p.pTile * (2 * NV);
+#pragma unroll 4
     for (int b = br.x; b <= br.y; ++b) {                     // the bands that feed this row, in band order
-      const int slot = dy - __ldg(wsi + p.t.rowD[s] + b * RB);
-      const float* e = parts + ((((size_t)n * p.nbands + b) * p.pTile + p.pOff[s] + (size_t)slot * oW + dx)) * NV;
-      add_entry<NV>(acc, e);
+      const float* e = base + b * bstride + (size_t)(dy - dfirst[b]) * oW * (2 * NV);
+      add_entry<NV>(acc, e);                                 // A part of this column's own interval
+      if (dx > 0) add_entry<NV>(acc, e - NV);                // B part of the interval to its left
     }
     const float tot = __ldg(ws + p.t.totY[s] + dy) * __ldg(ws + p.t.totX[s] + dx);
     const size_t o = (((size_t)n * oH + dy) * oW + dx) * CT;
@@ -479,13 +472,12 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   if (C != 1 && C != 2) return false;
   const int px = 4 / C;
   if (iW % px != 0 || iW < px) return false;
-  const int nthr = (((iW / px) + 31) / 32) * 32;
-  if (nthr > 512) return false;
   if (ns < 1 || ns > MS || N > 65535) return false;
+  const int P = C == 2 ? 10 : 12;                  // pixels per lane and row at most (NVEC 16-byte vectors)
   p.N = N; p.iH = iH; p.iW = iW; p.ns = ns;
   p.nbands = (iH + RB - 1) / RB;
-  p.nthr = nthr;
-  int words = 0, pt = 0, blk = 0;
+  if (p.nbands > MAXBANDS) return false;
+  int words = 0, pt = 0, blk = 0, thr = 0;
   auto take = [&](int n) { const int at = words; words += (n + 3) / 4 * 4; return at; };   // 16-byte aligned tables
   for (int s = 0; s < ns; ++s) {
     const int oH = out_hw[2 * s], oW = out_hw[2 * s + 1];
@@ -496,24 +488,33 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
     // the walk never skips an output row, whatever the rounding of the centres
     if (!(p.hs[s] >= 1.5f) || !(p.ws[s] >= 1.5f)) return false;
     p.maxRows[s] = (int)((float)(RB - 1) / p.hs[s]) + 3;
-    int J = 1;   // the CTA's threads are dealt out J to an output column
-    while (J < 32 && J * 2 * oW <= nthr) J *= 2;
-    p.J[s] = J;
+    // an interval holds at most floor(ws) + 1 columns; its first lane starts up to px - 1 columns before it
+    const int span = (int)p.ws[s] + 2 + (px - 1);
+    int J = 1, L = 0;
+    for (;; J *= 2) {
+      L = ((span + J - 1) / J + px - 1) / px * px;
+      if (L <= P) break;
+      if (J == 32) return false;
+    }
+    p.J[s] = J; p.L[s] = L;
+    p.tOff[s] = thr;
+    thr += (oW * J + 31) / 32 * 32;
     p.pOff[s] = pt;
     pt += p.maxRows[s] * oW;
     p.blkOff[s] = blk;
     blk += (oH * oW + CB - 1) / CB;
   }
-  for (int s = ns; s < MS; ++s) {   // unused scales: harmless values (their weights are zero, they are never flushed)
-    p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.maxRows[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
+  if (thr > 1024) return false;
+  p.nthr = thr;
+  for (int s = ns; s < MS; ++s) {   // unused scales
+    p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.L[s] = px; p.maxRows[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
   }
-  for (int s = ns; s <= MS; ++s) p.blkOff[s] = blk;
+  for (int s = ns; s <= MS; ++s) { p.blkOff[s] = blk; p.tOff[s] = thr; }
   p.pTile = pt;
-  // table area; the colS tables are packed back to back and followed by totX[0] (the band kernel copies them as one run)
+  // table area
   for (int s = 0; s < ns; ++s) { p.t.rowW[s] = take(2 * iH); p.t.rowD[s] = take(iH); }
   for (int s = 0; s < ns; ++s) p.t.colW[s] = take(2 * iW);
-  for (int s = 0; s < ns; ++s) { p.t.colS[s] = words; words += p.oW[s] + 1; }
-  words = (words + 3) / 4 * 4;
+  for (int s = 0; s < ns; ++s) p.t.colS[s] = take(p.oW[s] + 1);
   for (int s = 0; s < ns; ++s) p.t.totX[s] = take(p.oW[s]);
   for (int s = 0; s < ns; ++s) p.t.totY[s] = take(p.oH[s]);
   for (int s = 0; s < ns; ++s) p.t.bandR[s] = take(2 * p.oH[s]);
@@ -524,19 +525,19 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   if (nblocks > 0x7fffffffLL) return false;
   p.ctrlOff = align_up((size_t)words * 4, 256);
   p.partOff = align_up(p.ctrlOff + 16 + (size_t)nblocks * 4, 256);
-  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.pTile * (2 * C) * sizeof(float);
-  *band_smem = band_smem_layout(nthr, iW, p.t.totX[0] - p.t.colS[0]).total;
-  return *band_smem <= 200 * 1024;
+  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.pTile * (4 * C) * sizeof(float);
+  *band_smem = band_smem_layout(iW * C).total;
+  return *band_smem <= 100 * 1024;                 // the whole band stays resident (two CTAs per SM at least)
 }
 
 template <int CT>
 int ms_launch(const MsParams& p, size_t band_smem, const float* in, void* ws, cudaStream_t st) {
   static PerDeviceOnce once;   // per template instantiation; function attributes are per device
   const cudaError_t attr_err = per_device_once(once, [] {
-    cudaError_t e = cudaFuncSetAttribute(ms_band_kernel<CT, 256, DS_MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(ms_band_kernel<CT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         100 * 1024);
     if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(ms_band_kernel<CT, 512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      e = cudaFuncSetAttribute(ms_band_kernel<CT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     return e;
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
@@ -545,10 +546,10 @@ int ms_launch(const MsParams& p, size_t band_smem, const float* in, void* ws, cu
   int rc = after_launch();
   if (rc != FN2_OK) return rc;
   const dim3 grid((unsigned)p.nbands, (unsigned)p.N);
-  if (p.nthr <= 256)
-    ms_band_kernel<CT, 256, DS_MINB><<<grid, p.nthr, band_smem, st>>>(p, in, w);
+  if (p.in_scale == 1.0f)
+    ms_band_kernel<CT, false><<<grid, p.nthr, band_smem, st>>>(p, in, w);
   else
-    ms_band_kernel<CT, 512, 1><<<grid, p.nthr, band_smem, st>>>(p, in, w);
+    ms_band_kernel<CT, true><<<grid, p.nthr, band_smem, st>>>(p, in, w);
   rc = after_launch();
   if (rc != FN2_OK) return rc;
   ms_combine_kernel<CT><<<(unsigned)(p.N * p.blkOff[p.ns]), CB, 0, st>>>(p, w);

@@ -89,6 +89,111 @@ __device__ __forceinline__ Taps make_taps(float fx, float fy, int x, int y, int 
   return t;
 }
 
+// Image-gradient scatter window: a smaller margin than the gather window.  Scattered atomics cost about one lane per
+// clock whatever unit executes them (shared-memory fp32 adds are LDS + ATOMS.CAST.SPIN, two lane operations per value);
+// a tap outside the window costs FEWER lane operations as 8-byte global reductions (red.global.add.v2.f32, two floats
+// per lane operation) than one inside, and a smaller window is cheaper to zero and to flush, so the window only has to
+// catch the taps whose flush would otherwise be a scattered reduction per float: measured (tools/mb/mb_scatter.cu,
+// batch 32, flows ~ N(0, 8 px)): margins 22x24 0.195 ms, 16x16 0.164, 12x12 0.152, 8x8 0.142, 4x4 0.137; the same
+// ranking for sigma 2 and 0.5.
+template <int C>
+struct Scat {
+  static constexpr int MY = 8, MX = 8;                              // MX % 4 == 0: window rows start 16-byte aligned
+  static constexpr int ROWS = TH + 2 * MY + 1;
+  static constexpr int COLS = (TW + 2 * MX + 1 + 3) / 4 * 4;
+  static constexpr int RF = COLS * C;                               // floats per window row
+  static constexpr int FLOATS = ROWS * RF;
+  static_assert(FLOATS * 4 <= (int)Win<C>::BYTES - 128, "the scatter window lives in the gather window's buffer");
+};
+
+// adds v[0 .. 2C) to the 2C consecutive floats at p (left and right tap of one image row): 8-byte reductions for the
+// aligned pairs, scalar ones for a ragged first / last float
+template <int C>
+__device__ __forceinline__ void red_run(float* p, const float (&v)[2 * C]) {
+  if ((reinterpret_cast<uintptr_t>(p) & 7u) == 0) {
+#pragma unroll
+    for (int k = 0; k < C; ++k) atomicAdd(reinterpret_cast<float2*>(p) + k, make_float2(v[2 * k], v[2 * k + 1]));
+  } else {
+    atomicAdd(p, v[0]);
+#pragma unroll
+    for (int k = 0; k < C - 1; ++k)
+      atomicAdd(reinterpret_cast<float2*>(p + 1) + k, make_float2(v[2 * k + 1], v[2 * k + 2]));
+    atomicAdd(p + 2 * C - 1, v[2 * C - 1]);
+  }
+}
+
+// The four-tap scatter of one pixel's incoming gradient (flow_warp_grad.cu.cc:43-53): into the zeroed shared-memory
+// window `win` (origin wy0, wx0) when all four taps fall inside it, else straight to global memory.
+template <int C>
+__device__ __forceinline__ void scatter_taps(const Taps& tp, const float* gv, float* win, int wy0, int wx0,
+                                             float* gimg, int W) {
+  const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
+  const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
+  const bool inwin = (tp.T >= wy0) && (tp.B < wy0 + Scat<C>::ROWS) && (tp.L >= wx0) && (tp.R < wx0 + Scat<C>::COLS);
+  if (inwin) {
+    float* pL = win + (tp.T - wy0) * Scat<C>::RF + (tp.L - wx0) * C;
+    float* pR = win + (tp.T - wy0) * Scat<C>::RF + (tp.R - wx0) * C;
+    const int dB = (tp.B - tp.T) * Scat<C>::RF;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const float gc = gv[c];
+      atomicAdd(pL + c, gc * cTL);
+      atomicAdd(pR + c, gc * cTR);
+      atomicAdd(pL + dB + c, gc * cBL);
+      atomicAdd(pR + dB + c, gc * cBR);
+    }
+  } else if (tp.R == tp.L + 1) {
+    // the left and right tap of a row are 2C consecutive floats
+    float vt[2 * C], vb[2 * C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      vt[c] = gv[c] * cTL; vt[C + c] = gv[c] * cTR;
+      vb[c] = gv[c] * cBL; vb[C + c] = gv[c] * cBR;
+    }
+    float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;
+    red_run<C>(pT, vt);
+    red_run<C>(pT + (size_t)(tp.B - tp.T) * W * C, vb);    // B == T (last image row): the same floats again, as the
+  } else {                                                  // reference's two atomics to one address
+    float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;      // R == L: last image column
+    const size_t dB = (size_t)(tp.B - tp.T) * W * C;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+      const float gc = gv[c];
+      atomicAdd(pT + c, gc * cTL);
+      atomicAdd(pT + c, gc * cTR);
+      atomicAdd(pT + dB + c, gc * cBL);
+      atomicAdd(pT + dB + c, gc * cBR);
+    }
+  }
+}
+
+// zero the scatter window / flush it: every window row inside the image is one bulk reduce-add
+// (cp.reduce.async.bulk .add.f32, executed by the copy engine: no LSU instructions), clipped to the image; offsets and
+// sizes stay multiples of 16 bytes because W*C, MX*C and the window width are multiples of 4 floats.
+template <int C>
+__device__ __forceinline__ void scatter_zero(float* win) {
+  for (int i = threadIdx.x; i < Scat<C>::FLOATS / 4; i += NT) reinterpret_cast<float4*>(win)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+template <int C>
+__device__ __forceinline__ void scatter_flush(const float* win, float* gimage, int n, int H, int W, int wy0, int wx0) {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the async proxy
+  __syncthreads();
+  if (threadIdx.x < Scat<C>::ROWS) {
+    const int r = threadIdx.x;
+    const int yy = wy0 + r;
+    const int fc0 = wx0 * C;
+    const int lo = max(fc0, 0), hi = min(fc0 + Scat<C>::RF, W * C);
+    if (yy >= 0 && yy < H && hi > lo) {
+      float* dst = gimage + ((size_t)n * H + yy) * W * C + lo;
+      const uint32_t src = smem_u32(win + r * Scat<C>::RF + (lo - fc0));
+      asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
+                   ::"l"(dst), "r"(src), "r"((uint32_t)(hi - lo) * 4u) : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory stays valid until it was read
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ forward
 // MODE 0: out = warp(image, flow).   MODE 1: flow gradient (needs gout), same gather.
 // MODE 2: MODE 0 plus the brightness error of the stacked nets (flownet_cs.py:24-27, flownet2.py:33-39): gout is
@@ -246,8 +351,8 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_scatter(const float* __restri
       gv[4 * v] = q.x; gv[4 * v + 1] = q.y; gv[4 * v + 2] = q.z; gv[4 * v + 3] = q.w;
     }
   }
-  for (int i = threadIdx.x; i < Win<C>::NB * Win<C>::BOX_FLOATS / 4; i += NT)
-    reinterpret_cast<float4*>(win)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int sy0 = t.ty0 - Scat<C>::MY, sx0 = t.tx0 - Scat<C>::MX;
+  scatter_zero<C>(win);
   __syncthreads();
 
   if (live) {
@@ -255,57 +360,10 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_scatter(const float* __restri
 #pragma unroll
     for (int i = 0; i < PXT; ++i) {
       const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
-      if (!tp.in) continue;
-      const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
-      const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
-      const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
-                         (tp.R < t.wx0 + Win<C>::COLS);
-      if (inwin) {
-        float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
-        float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
-        const int dB = (tp.B - tp.T) * Win<C>::BW;
-#pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const float gc = gv[i * C + c];
-          atomicAdd(pL + c, gc * cTL);
-          atomicAdd(pR + c, gc * cTR);
-          atomicAdd(pL + dB + c, gc * cBL);
-          atomicAdd(pR + dB + c, gc * cBR);
-        }
-      } else {
-        float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;
-        const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
-#pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const float gc = gv[i * C + c];
-          atomicAdd(pT + c, gc * cTL);
-          atomicAdd(pT + dR + c, gc * cTR);
-          atomicAdd(pT + dB + c, gc * cBL);
-          atomicAdd(pT + dB + dR + c, gc * cBR);
-        }
-      }
+      if (tp.in) scatter_taps<C>(tp, gv + i * C, win, sy0, sx0, gimg, W);
     }
   }
-
-  // flush: every window row inside the image is one bulk reduce-add (cp.reduce.async.bulk .add.f32, executed by the
-  // copy engine: no LSU instructions), clipped to the image; offsets and sizes stay multiples of 16 bytes because
-  // W*C, MX*C and the box width are multiples of 4 floats.
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the async proxy
-  __syncthreads();
-  if (threadIdx.x < Win<C>::NB * Win<C>::ROWS) {
-    const int b = threadIdx.x / Win<C>::ROWS, r = threadIdx.x - b * Win<C>::ROWS;
-    const int yy = t.wy0 + r;
-    const int fc0 = t.wx0 * C + b * Win<C>::BW;
-    const int lo = max(fc0, 0), hi = min(fc0 + Win<C>::BW, W * C);
-    if (yy >= 0 && yy < H && hi > lo) {
-      float* dst = gimage + ((size_t)t.n * H + yy) * W * C + lo;
-      const uint32_t src = smem_u32(win + b * Win<C>::BOX_FLOATS + r * Win<C>::BW + (lo - fc0));
-      asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
-                   ::"l"(dst), "r"(src), "r"((uint32_t)(hi - lo) * 4u) : "memory");
-    }
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory stays valid until it was read
-  }
+  scatter_flush<C>(win, gimage, t.n, H, W, sy0, sx0);
 }
 
 // ------------------------------------------------------------------------------------- backward: both gradients
@@ -404,62 +462,20 @@ __global__ void __launch_bounds__(NT, 2) warp_tile_bwd(const __grid_constant__ C
   }
   __syncthreads();   // everyone has read the image window
 
-  // ---- phase 2: image gradient (flow_warp_grad.cu.cc:43-53): the window, zeroed, collects the scatter ----
-  for (int i = threadIdx.x; i < Win<C>::NB * Win<C>::BOX_FLOATS / 4; i += NT)
-    reinterpret_cast<float4*>(win)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  // ---- phase 2: image gradient (flow_warp_grad.cu.cc:43-53): a (smaller) window in the same buffer, zeroed, collects
+  // the scatter ----
+  const int sy0 = t.ty0 - Scat<C>::MY, sx0 = t.tx0 - Scat<C>::MX;
+  scatter_zero<C>(win);
   __syncthreads();
   if (live) {
     float* gimg = gimage + (size_t)t.n * H * W * C;
 #pragma unroll
     for (int i = 0; i < PXT; ++i) {
       const Taps tp = make_taps(f[i].x, f[i].y, x + i, y, W, H);
-      if (!tp.in) continue;
-      const float cTL = (1 - tp.alpha) * (1 - tp.beta), cTR = tp.alpha * (1 - tp.beta);
-      const float cBL = (1 - tp.alpha) * tp.beta, cBR = tp.alpha * tp.beta;
-      const bool inwin = (tp.T >= t.wy0) && (tp.B < t.wy0 + Win<C>::ROWS) && (tp.L >= t.wx0) &&
-                         (tp.R < t.wx0 + Win<C>::COLS);
-      if (inwin) {
-        float* pL = win + Win<C>::at(tp.T - t.wy0, tp.L - t.wx0);
-        float* pR = win + Win<C>::at(tp.T - t.wy0, tp.R - t.wx0);
-        const int dB = (tp.B - tp.T) * Win<C>::BW;
-#pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const float gc = gv[i * C + c];
-          atomicAdd(pL + c, gc * cTL);
-          atomicAdd(pR + c, gc * cTR);
-          atomicAdd(pL + dB + c, gc * cBL);
-          atomicAdd(pR + dB + c, gc * cBR);
-        }
-      } else {
-        float* pT = gimg + ((size_t)tp.T * W + tp.L) * C;
-        const size_t dR = (size_t)(tp.R - tp.L) * C, dB = (size_t)(tp.B - tp.T) * W * C;
-#pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const float gc = gv[i * C + c];
-          atomicAdd(pT + c, gc * cTL);
-          atomicAdd(pT + dR + c, gc * cTR);
-          atomicAdd(pT + dB + c, gc * cBL);
-          atomicAdd(pT + dB + dR + c, gc * cBR);
-        }
-      }
+      if (tp.in) scatter_taps<C>(tp, gv + i * C, win, sy0, sx0, gimg, W);
     }
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the async proxy
-  __syncthreads();
-  if (threadIdx.x < Win<C>::NB * Win<C>::ROWS) {
-    const int b = threadIdx.x / Win<C>::ROWS, r = threadIdx.x - b * Win<C>::ROWS;
-    const int yy = t.wy0 + r;
-    const int fc0 = t.wx0 * C + b * Win<C>::BW;
-    const int lo = max(fc0, 0), hi = min(fc0 + Win<C>::BW, W * C);
-    if (yy >= 0 && yy < H && hi > lo) {
-      float* dst = gimage + ((size_t)t.n * H + yy) * W * C + lo;
-      const uint32_t src = smem_u32(win + b * Win<C>::BOX_FLOATS + r * Win<C>::BW + (lo - fc0));
-      asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;"
-                   ::"l"(dst), "r"(src), "r"((uint32_t)(hi - lo) * 4u) : "memory");
-    }
-    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // shared memory stays valid until it was read
-  }
+  scatter_flush<C>(win, gimage, t.n, H, W, sy0, sx0);
 }
 
 template <int C>

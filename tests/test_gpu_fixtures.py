@@ -73,18 +73,26 @@ def test_flow_warp_backward_on_the_sample_pair(sample):
 
 @pytest.mark.parametrize("scale", [1.0, 0.05])
 def test_downsample_of_the_ground_truth_flow_all_loss_scales(sample, scale):
+    """Real flows reach 109 px and the coarsest scale averages 153 x 147 samples: the reference's own sequential
+    fp32 sum is 8.5e-5 away from the exact value there (C restatement vs the float64 restatement, which agree with the
+    reference kernel / with exact arithmetic respectively), so the value check is against the float64 oracle, with the
+    absolute term scaled by the data (5e-7 * max|x|), and the fp32-order comparisons get 2e-6 * max|x|."""
     _, _, flow = sample
     fs = (flow * scale).contiguous()       # the loss downsamples flow * 0.05 (flownet_c.py:128)
+    mag = float(fs.abs().max())
     single = [fn2.downsample(fs.cuda(), list(s)) for s in LOSS_SIZES]
     multi = fn2.downsample_multi(fs.cuda(), LOSS_SIZES)
     for size, a, b in zip(LOSS_SIZES, single, multi):
+        exact = o.np_downsample(fs.numpy(), size)
+        assert_close(a.cpu().numpy(), exact, rel=1e-5, abs_=5e-7 * mag, what="downsample %s vs float64" % (size,))
+        assert_close(b.cpu().numpy(), exact, rel=1e-5, abs_=5e-7 * mag, what="downsample_multi %s vs float64" % (size,))
         want = o.c_downsample(fs.numpy(), size)
-        assert_close(a.cpu().numpy(), want, rel=1e-5, abs_=5e-6, what="downsample %s" % (size,))
-        assert_close(b.cpu().numpy(), want, rel=1e-5, abs_=5e-6, what="downsample_multi %s" % (size,))
+        assert_close(b.cpu().numpy(), want, rel=1e-5, abs_=2e-6 * mag, what="downsample_multi %s vs fp32 order" % (size,))
         if ref.available():
             r = ref.downsample(fs.cuda(), size)
             torch.cuda.synchronize()
-            assert_close(b.cpu().numpy(), r.cpu().numpy(), rel=1e-5, abs_=5e-6, what="vs reference kernel %s" % (size,))
+            assert_close(want, r.cpu().numpy(), rel=1e-5, abs_=2e-7 * mag, what="oracle vs reference kernel %s" % (size,))
+            assert_close(b.cpu().numpy(), r.cpu().numpy(), rel=1e-5, abs_=2e-6 * mag, what="vs reference kernel %s" % (size,))
 
 
 def test_multiscale_epe_on_the_ground_truth_flow(sample):
@@ -94,6 +102,6 @@ def test_multiscale_epe_on_the_ground_truth_flow(sample):
     epe = fn2.multiscale_epe(flow.cuda(), [p.cuda() for p in preds], 0.05)
     fs = (flow * 0.05).numpy()
     for k, (size, p) in enumerate(zip(LOSS_SIZES, preds)):
-        d = o.c_downsample(fs, size).astype(np.float64)
+        d = o.np_downsample(fs, size).astype(np.float64)
         want = np.sqrt(((p.numpy() - d) ** 2).sum(-1)).sum() / 1.0     # utils.py:219-224
         assert abs(float(epe[k]) - want) <= 1e-5 * abs(want) + 1e-5, (size, float(epe[k]), want)
