@@ -10,7 +10,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfn2ops.so")
+# FN2_OPS_LIBRARY: developer override, to time a variant build of the same ABI (never a fallback: the file must exist)
+LIB_PATH = os.environ.get("FN2_OPS_LIBRARY") or os.path.join(_HERE, "libfn2ops.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
 PRECISIONS = {"fp32": 0, "tf32": 1, "tf32x3": 3}

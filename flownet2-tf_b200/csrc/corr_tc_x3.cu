@@ -41,7 +41,10 @@ constexpr int A_CHUNK = 2 * A_HALF;     // M = 128 operand rows of one 32-channe
 constexpr int BROWS = 2;                // b-rows per block
 constexpr int B_HALF = BROWS * 32 * 128;   // 64 b-pixels x 32 channels = 8 KB (raw; the lo copy follows it)
 constexpr int B_STAGE = 2 * B_HALF;     // N = 128 operand rows of one 32-channel chunk
-constexpr int NSTAGE = 4;               // B ring depth
+#ifndef X3_NSTAGE
+#define X3_NSTAGE 4
+#endif
+constexpr int NSTAGE = X3_NSTAGE;       // B ring depth
 constexpr int NBUF = 4;                 // TMEM accumulator buffers (4 x 128 columns = 512)
 constexpr int BUF_COLS = 2 * BROWS * 32;
 constexpr int MAX_KC = 8;               // C <= 256
@@ -59,6 +62,7 @@ struct X3Params {
   int Hcb[2];         // class-space rows of b (>= Hc + boff when b carries row halos)
   int boff;           // class-space row of b that a-row 0 meets at displacement 0
   int TY, TX;
+  int TYP, nwork;     // CTA-pair kernel: pair tiles (4 a-rows) per class, length of the work list
   int nkc;            // C / 32
   float sumelems;
   int opitch;         // floats between consecutive pixels of the output
@@ -346,6 +350,316 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_fwd_x3_kernel(const __gri
   }
 }
 
+// ---- CTA-pair version (cta_group::2), narrow images (one 32-column tile per class: the FlowNetC shape) ----------------
+// A single-CTA M128 N128 K8 SS-form MMA reads 8 KB of shared memory per 64 tensor clocks, the SM's whole 128 B/clk,
+// and the converters' and TMA's traffic comes on top: the kernel above is bound by shared-memory bandwidth at ~40 % of
+// the tensor rate.  Here two CTAs of a cluster own FOUR consecutive class-rows of a (two each: M = 256 = 2 x [64 raw +
+// 64 lo]) and share every streamed block of FOUR b-rows (N = 256 = 2 x [64 raw + 64 lo]): each CTA loads and splits
+// only ITS two b-rows, and one tcgen05.mma.cta_group::2 M256 N256 K8 (128 tensor clocks) reads 4 KB of A + 4 KB of B
+// per CTA -- 64 B/clk, plus 32 B/clk of conversion and 16 B/clk of TMA fill.  Accumulator: 128 lanes x 256 columns per
+// CTA and block, two buffers.  Column n of a block: CTA (n / 128)'s b-rows, inside them [64 raw | 64 lo] x
+// [b-row 0 | b-row 1] x 32 columns.  Persistent like corr_tc_fwd_pair_kernel (corr_tc.cu): a pair strides over the
+// work list, every barrier's phase carries over, the next tile's a chunks load and split under the last block.
+// Barriers: full / a_full are local (each CTA's converters wait for their own TMA); conv / a_conv live in the leader
+// and collect BOTH CTAs' converter warps (the issuer's only wait before the MMAs); empty / a_free / tmem_full are
+// multicast commits; tmem_empty lives in the leader and collects both CTAs' epilogue warps.
+constexpr int PR = 2;                   // a-rows per CTA
+constexpr int PBROWS = 4;               // b-rows per block (two per CTA)
+constexpr int PNBUF = 2;                // accumulator buffers of 256 columns
+constexpr int PBUF_COLS = 256;
+constexpr int PNEPI = 8;                // epilogue warps: two per TMEM lane quadrant, one per CTA-half of the block
+constexpr int PNTHREADS = 64 + 32 * PNEPI + 32 * NCONV;
+
+struct __align__(8) X3PairBarriers {
+  uint64_t a_full[MAX_KC];    // local: raw chunk kc of this CTA's a tile has landed
+  uint64_t a_conv[MAX_KC];    // leader: both CTAs' lo halves of chunk kc are written
+  uint64_t a_free[MAX_KC];    // local (multicast commit): the tile's last block has read chunk kc
+  uint64_t full[NSTAGE];      // local: this CTA's raw half of the b chunk landed
+  uint64_t conv[NSTAGE];      // leader: both CTAs' lo halves written
+  uint64_t empty[NSTAGE];     // local (multicast commit)
+  uint64_t tmem_full[PNBUF];  // local (multicast commit)
+  uint64_t tmem_empty[PNBUF]; // leader: both CTAs' epilogue warps
+  uint32_t tmem_base;
+};
+
+struct X3Work {
+  int n, cls, cy, cx, Hc, Wc, Hcb, y0p, s_first, nblk;
+  bool valid;
+};
+template <int R>
+__device__ __forceinline__ X3Work x3_work(const X3Params& P, int w) {
+  X3Work k;
+  int t = w;
+  const int typ = t % P.TYP; t /= P.TYP;
+  k.cls = t % P.ncls;
+  k.n = t / P.ncls;
+  k.cy = k.cls / P.s2; k.cx = k.cls % P.s2;
+  k.Hc = P.Hc[k.cy]; k.Wc = P.Wc[k.cx]; k.Hcb = P.Hcb[k.cy];
+  k.y0p = typ * 2 * PR;
+  k.nblk = 0; k.s_first = 0;
+  k.valid = !(k.y0p >= k.Hc || k.Wc < 1);
+  if (!k.valid) return k;
+  const int ylast = min(k.y0p + 2 * PR - 1, k.Hc - 1);
+  k.s_first = max(0, k.y0p + P.boff - R);
+  const int s_last = min(k.Hcb - 1, ylast + P.boff + R);
+  k.nblk = max(0, (s_last - k.s_first + PBROWS) / PBROWS);
+  return k;
+}
+
+template <int R>
+__global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const __grid_constant__ X3Params P) {
+  constexpr int GW = 2 * R + 1;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + (size_t)P.nkc * A_CHUNK;
+  float* sStage = reinterpret_cast<float*>(sB + (size_t)NSTAGE * B_STAGE);
+  X3PairBarriers* bars = reinterpret_cast<X3PairBarriers*>(sStage + PNEPI * STG_FLOATS);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair0 = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int nkc = P.nkc;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < MAX_KC; ++i) {
+      mbar_init(smem_u32(&bars->a_full[i]), 1);
+      mbar_init(smem_u32(&bars->a_conv[i]), 2 * NCONV);
+      mbar_init(smem_u32(&bars->a_free[i]), 1);
+    }
+    for (int i = 0; i < NSTAGE; ++i) {
+      mbar_init(smem_u32(&bars->full[i]), 1);
+      mbar_init(smem_u32(&bars->conv[i]), 2 * NCONV);
+      mbar_init(smem_u32(&bars->empty[i]), 1);
+    }
+    for (int i = 0; i < PNBUF; ++i) {
+      mbar_init(smem_u32(&bars->tmem_full[i]), 1);
+      mbar_init(smem_u32(&bars->tmem_empty[i]), 2 * PNEPI);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc_pair(smem_u32(&bars->tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // the peer's barriers exist before anything is signalled on them
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0) {
+    // ================================ TMA producer (both CTAs, each its own rows) ================================
+    if (elect_one()) {
+      int it = 0, used = 0;
+      for (int w = pair0; w < P.nwork; w += npairs) {
+        const X3Work k = x3_work<R>(P, w);
+        if (k.nblk == 0) continue;
+        const int y0 = k.y0p + (int)rank * PR;
+        const int ya = y0 < k.Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
+        for (int blk = 0; blk < k.nblk; ++blk) {
+          const int srow = k.s_first + blk * PBROWS + BROWS * (int)rank;   // this CTA's two b-rows of the block
+          for (int kc = 0; kc < nkc; ++kc, ++it) {
+            if (blk == 0) {   // the a tile goes out chunk by chunk, interleaved with block 0 which consumes it in this order
+              if (used > 0) mbar_wait(smem_u32(&bars->a_free[kc]), (used - 1) & 1);   // the previous tile is done with it
+              const uint32_t a_full = smem_u32(&bars->a_full[kc]);
+              mbar_expect_tx(a_full, A_HALF);
+              tma_load_4d(smem_u32(sA + (size_t)kc * A_CHUNK), &P.a[k.cls], a_full, kc * KCH, 0, ya, k.n);
+            }
+            const int stage = it % NSTAGE;
+            mbar_wait(smem_u32(&bars->empty[stage]), ((it / NSTAGE) & 1) ^ 1);
+            const uint32_t full = smem_u32(&bars->full[stage]);
+            mbar_expect_tx(full, B_HALF);
+            tma_load_4d(smem_u32(sB + (size_t)stage * B_STAGE), &P.b[k.cls], full, kc * KCH, 0, srow, k.n);
+          }
+        }
+        ++used;
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (leader only) ================================
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = idesc_tf32(256, PBUF_COLS);
+      int it = 0, gb = 0, used = 0;
+      for (int w = pair0; w < P.nwork; w += npairs) {
+        const X3Work k = x3_work<R>(P, w);
+        if (k.nblk == 0) continue;
+        for (int blk = 0; blk < k.nblk; ++blk, ++gb) {
+          const int buf = gb % PNBUF;
+          mbar_wait(smem_u32(&bars->tmem_empty[buf]), ((gb / PNBUF) & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)buf * PBUF_COLS;
+          for (int kc = 0; kc < nkc; ++kc, ++it) {
+            const int stage = it % NSTAGE;
+            if (blk == 0) mbar_wait(smem_u32(&bars->a_conv[kc]), used & 1);
+            mbar_wait(smem_u32(&bars->conv[stage]), (it / NSTAGE) & 1);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(sA + (size_t)kc * A_CHUNK);
+            const uint32_t b_addr = smem_u32(sB + (size_t)stage * B_STAGE);
+#pragma unroll
+            for (int k4 = 0; k4 < 4; ++k4)
+              umma_tf32_pair(d_tmem, desc_sw128_kmajor(a_addr + k4 * 32), desc_sw128_kmajor(b_addr + k4 * 32), idesc,
+                             (uint32_t)((kc | k4) != 0));
+            umma_commit_pair(smem_u32(&bars->empty[stage]), 3);   // frees the stage (raw and lo) in both CTAs
+            if (blk == k.nblk - 1) umma_commit_pair(smem_u32(&bars->a_free[kc]), 3);   // a chunk kc may be replaced
+          }
+          umma_commit_pair(smem_u32(&bars->tmem_full[buf]), 3);   // accumulator block complete in both CTAs
+        }
+        ++used;
+      }
+    }
+  } else if (warp < 2 + PNEPI) {
+    // ================================ epilogue (warps 2..9, both CTAs) ================================
+    const int ew = warp - 2;
+    const int q = warp & 3;              // TMEM lane quadrant this warp may read
+    const int ar = q & 1;                // a-row of this CTA's tile
+    const int isLo = q >> 1;             // quadrants 2, 3 hold the products of a_lo
+    const int half = ew >> 2;            // which CTA's b-rows of a block (columns half * 128 ...) this warp works on
+    // The hi warp and the lo warp of (a-row, half) share two staging tiles: tile 0 collects b-row 0 of the half
+    // (finished by the hi warp), tile 1 b-row 1 (finished by the lo warp).
+    const int grp = ar * 2 + half;
+    float* mine = sStage + (grp * 2 + isLo) * STG_FLOATS;
+    float* theirs = sStage + (grp * 2 + (isLo ^ 1)) * STG_FLOATS;
+    const float inv = 1.0f / P.sumelems;
+    const int pixstride = P.s2 * P.opitch;
+    const uint32_t tmem_empty0 = mapa_u32(smem_u32(&bars->tmem_empty[0]), 0);
+
+    // Store plan of one displacement row (32 pixels x GW values, 84-byte runs, written coalesced): element e =
+    // tt * 32 + lane is value o = e % GW of pixel column cc = e / GW and comes from b column xb = cc + o - R (a zero
+    // when that column is outside the class row).  Recomputed per store: a table of GW registers costs more here.
+    int gb = 0;
+    for (int w = pair0; w < P.nwork; w += npairs) {
+      const X3Work k = x3_work<R>(P, w);
+      if (!k.valid) continue;
+      const int y = k.y0p + (int)rank * PR + ar;
+      const bool row_ok = y < k.Hc;
+      const int Y = y * P.s2 + k.cy;
+      const int ncol = min(TILE_C, k.Wc);
+      float* orow0 = P.out + (((size_t)k.n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)k.cx) * P.opitch;
+
+      if (row_ok) {   // displacement rows that point outside the image: zeros, never computed
+        const int yb = y + P.boff;
+        const int dlo = min(GW, max(0, R - yb)) * GW;
+        const int dhi = max(0, min(GW, k.Hcb - yb + R)) * GW;
+        for (int cc = isLo + 2 * half; cc < ncol; cc += 4) {
+          float* po = orow0 + (size_t)cc * pixstride;
+          for (int e = lane; e < dlo; e += 32) po[e] = 0.f;
+          for (int e = dhi + lane; e < P.D; e += 32) po[e] = 0.f;
+        }
+      }
+
+      for (int blk = 0; blk < k.nblk; ++blk, ++gb) {
+        const int buf = gb % PNBUF;
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), (gb / PNBUF) & 1);
+        tc_fence_after();
+        const int sbase = k.s_first + blk * PBROWS + BROWS * half;
+        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * PBUF_COLS + half * 128);
+        {
+          const int brMine = isLo, brTheirs = isLo ^ 1;
+          const int sM = sbase + brMine, sT = sbase + brTheirs;
+          const int pM = sM - (y + P.boff), pT = sT - (y + P.boff);
+          const bool okM = row_ok && pM >= -R && pM <= R && sM < k.Hcb;   // the same in both warps of the pair
+          const bool okT = row_ok && pT >= -R && pT <= R && sT < k.Hcb;
+          float vm[32];
+          if (okT) {   // the partner finishes this b-row: hand it this warp's partial sum
+            float v[32];
+            tmem_ld32_sum2(tbase + (uint32_t)(brTheirs * 32), v);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) theirs[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+          }
+          if (okM) tmem_ld32_sum2(tbase + (uint32_t)(brMine * 32), vm);
+          named_bar_sync(1 + grp, 64);     // both partial sums are in the tiles
+          if (okM) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) mine[j * 33 + lane] += vm[j];   // same lane, same word the partner wrote
+            __syncwarp();
+            float* orow = orow0 + (pM + R) * GW;
+            // loads in batches of 7 ahead of their stores: a load -> scale -> store chain per value left the warp
+            // waiting on shared-memory latency 21 times per row (48 % of the epilogue's stall samples)
+#pragma unroll
+            for (int t0 = 0; t0 < GW; t0 += 7) {
+              float xv[7];
+#pragma unroll
+              for (int u = 0; u < 7; ++u) {
+                const int e = (t0 + u) * 32 + lane;
+                const int cc = e / GW, xb = cc + (e - cc * GW) - R;
+                xv[u] = mine[(xb & 31) * 33 + cc];
+              }
+#pragma unroll
+              for (int u = 0; u < 7; ++u) {
+                const int e = (t0 + u) * 32 + lane;
+                const int cc = e / GW, o = e - cc * GW;
+                const int xb = cc + o - R;
+                float x = (xb >= 0 && xb < 32) ? xv[u] * inv : 0.f;
+                x = x > 0.f ? x : x * P.slope;
+                if (cc < ncol) orow[cc * pixstride + o] = x;
+              }
+            }
+          }
+          named_bar_sync(1 + grp, 64);     // the tiles may be overwritten
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(tmem_empty0 + (uint32_t)buf * 8u);
+      }
+    }
+  } else {
+    // ================================ converters (warps 10..13, both CTAs): lo = x - tf32(x) ====================
+    const int ct = threadIdx.x - (64 + 32 * PNEPI);
+    constexpr int NCT = 32 * NCONV;
+    const uint32_t a_conv0 = mapa_u32(smem_u32(&bars->a_conv[0]), 0);
+    const uint32_t conv0 = mapa_u32(smem_u32(&bars->conv[0]), 0);
+    int it = 0, used = 0;
+    for (int w = pair0; w < P.nwork; w += npairs) {
+      const X3Work k = x3_work<R>(P, w);
+      if (k.nblk == 0) continue;
+      for (int blk = 0; blk < k.nblk; ++blk) {
+        for (int kc = 0; kc < nkc; ++kc, ++it) {
+          if (blk == 0) {
+            mbar_wait(smem_u32(&bars->a_full[kc]), used & 1);
+            uint8_t* base = sA + (size_t)kc * A_CHUNK;
+            float4 v[A_HALF / 16 / NCT];
+#pragma unroll
+            for (int i = 0; i < A_HALF / 16 / NCT; ++i) v[i] = *reinterpret_cast<const float4*>(base + (ct + i * NCT) * 16);
+#pragma unroll
+            for (int i = 0; i < A_HALF / 16 / NCT; ++i)
+              *reinterpret_cast<float4*>(base + A_HALF + (ct + i * NCT) * 16) = x3_lo4(v[i]);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the MMA
+            __threadfence_block();   // ... and ordered before the arrival below (a release at cluster scope costs a
+            __syncwarp();            // MEMBAR.GPU + ERRBAR per arrival: measured 16 % of all stall samples)
+            if (lane == 0) mbar_arrive_cluster(a_conv0 + (uint32_t)kc * 8u);
+          }
+          const int stage = it % NSTAGE;
+          mbar_wait(smem_u32(&bars->full[stage]), (it / NSTAGE) & 1);
+          uint8_t* base = sB + (size_t)stage * B_STAGE;
+          float4 v[B_HALF / 16 / NCT];
+#pragma unroll
+          for (int i = 0; i < B_HALF / 16 / NCT; ++i) v[i] = *reinterpret_cast<const float4*>(base + (ct + i * NCT) * 16);
+#pragma unroll
+          for (int i = 0; i < B_HALF / 16 / NCT; ++i)
+            *reinterpret_cast<float4*>(base + B_HALF + (ct + i * NCT) * 16) = x3_lo4(v[i]);
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __threadfence_block();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(conv0 + (uint32_t)stage * 8u);
+        }
+      }
+      ++used;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // neither CTA may go while the other can still touch its shared memory / barriers
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, 512);
+  }
+}
+
+size_t x3_pair_smem_bytes(int nkc) {
+  return 1024 + (size_t)nkc * A_CHUNK + (size_t)NSTAGE * B_STAGE + (size_t)PNEPI * STG_FLOATS * sizeof(float) +
+         sizeof(X3PairBarriers);
+}
+
 size_t x3_smem_bytes(int nkc) {
   return 1024 + (size_t)nkc * A_CHUNK + (size_t)NSTAGE * B_STAGE + (size_t)NEPI * STG_FLOATS * sizeof(float) +
          sizeof(X3Barriers);
@@ -390,6 +704,39 @@ int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float*
     return e;
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  P.TYP = (P.Hc[0] + 2 * PR - 1) / (2 * PR);
+  P.nwork = 0;
+  static PerDeviceOnce once_pair;
+  const EnvSwitches& sw = env_switches();
+  if (P.TX == 1 && !sw.no_pair) {
+    // narrow images: persistent CTA pairs over the list of 4-row pair tiles
+    const cudaError_t pe = per_device_once(once_pair, [] {
+      cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_x3_pair_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)x3_pair_smem_bytes(MAX_KC));
+      return e;
+    });
+    if (pe != cudaSuccess) { note_cuda_error(pe); (void)cudaGetLastError(); return FN2_E_CUDA; }
+    const long long nwork = (long long)g.N * P.ncls * P.TYP;
+    if (nwork > 0x3fffffffLL) return FN2_E_BAD_SHAPE;
+    P.nwork = (int)nwork;
+    const long long slots = std::max(1, device_sm_count() / 2);
+    const long long pgrid = 2 * (sw.no_persist ? nwork : std::min<long long>(nwork, slots));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pgrid);
+    cfg.blockDim = dim3(PNTHREADS);
+    cfg.dynamicSmemBytes = x3_pair_smem_bytes(P.nkc);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, corr_tc_fwd_x3_pair_kernel<10>, P);
+    if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
+    return after_launch();
+  }
   const long long grid = (long long)g.N * P.ncls * P.TY * P.TX;
   if (grid > 0x7fffffffLL) return FN2_E_BAD_SHAPE;
   const size_t smem = x3_smem_bytes(P.nkc);

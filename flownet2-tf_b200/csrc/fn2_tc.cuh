@@ -303,13 +303,12 @@ __host__ __device__ constexpr uint32_t idesc_tf32_major(int M, int N, int a_mn, 
 // "hi" operand: hi = x with those bits cleared.  lo = x - hi is exact in fp32 (at most 13 significant bits); it is
 // rounded to nearest on 11 significant bits here so that the tensor core's truncation of lo loses nothing more.
 //   x * y  ~=  hi_x*hi_y + lo_x*hi_y + hi_x*lo_y (+ lo_x*lo_y)      relative error ~2^-21 per product
-// Inf / NaN: hi carries them; lo must not turn inf into inf - inf = NaN.
+// Inf / NaN: hi carries them; lo is 0 there (it must not turn inf into inf - inf = NaN).
 __device__ __forceinline__ float x3_lo(float x) {
   const uint32_t u = __float_as_uint(x);
   float l = x - __uint_as_float(u & 0xffffe000u);
   l = __uint_as_float((__float_as_uint(l) + 0x1000u) & 0xffffe000u);
-  if ((u & 0x7f800000u) == 0x7f800000u) l = (u & 0x007fffffu) ? x : 0.f;
-  return l;
+  return fabsf(x) < __int_as_float(0x7f800000) ? l : 0.f;   // inf: not inf - inf; NaN: hi carries it (one FSETP + FSEL)
 }
 __device__ __forceinline__ float4 x3_lo4(float4 v) { return make_float4(x3_lo(v.x), x3_lo(v.y), x3_lo(v.z), x3_lo(v.w)); }
 
@@ -317,6 +316,17 @@ __device__ __forceinline__ float4 x3_lo4(float4 v) { return make_float4(x3_lo(v.
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled is a DRIVER call and needs a current context: a thread whose first CUDA action is one of
+// our launches (PyTorch's autograd worker running a backward) has none yet -- CUDA_ERROR_INVALID_CONTEXT.
+// cudaSetDevice on the runtime's current device binds the primary context to the calling thread; it is not a stream
+// operation, so it is legal during stream capture.
+inline void bind_context() {
+  thread_local int bound = -1;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return;
+  if (dev != bound && cudaSetDevice(dev) == cudaSuccess) bound = dev;
+}
 
 inline EncodeTiledFn get_encode() {
   static EncodeTiledFn fn = nullptr;
@@ -336,14 +346,17 @@ inline bool make_class_map(CUtensorMap* m, const float* base, int N, int H, int 
                     int Wc, int box_w, int box_h, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
+  bind_context();
   const cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)Wc, (cuuint64_t)Hc, (cuuint64_t)N};
   const cuuint64_t strides[3] = {(cuuint64_t)s2 * C * 4, (cuuint64_t)s2 * W * C * 4, (cuuint64_t)H * W * C * 4};
   const cuuint32_t box[4] = {KCH, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   void* addr = const_cast<float*>(base + ((size_t)cy * W + cx) * C);
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, addr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-             swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  const CUresult rc = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, addr, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) note_cuda_error(static_cast<cudaError_t>(100000 + (int)rc));   // driver error, offset 100000
+  return rc == CUDA_SUCCESS;
 }
 
 
@@ -352,13 +365,16 @@ inline bool make_class_map(CUtensorMap* m, const float* base, int N, int H, int 
 inline bool make_row_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int box_w, int box_h) {
   EncodeTiledFn enc = get_encode();
   if (!enc) return false;
+  bind_context();
   const cuuint64_t dims[3] = {(cuuint64_t)W * C, (cuuint64_t)H, (cuuint64_t)N};
   const cuuint64_t strides[2] = {(cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
   const cuuint32_t box[3] = {(cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   const cuuint32_t estr[3] = {1, 1, 1};
-  return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
-             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  const CUresult rc = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) note_cuda_error(static_cast<cudaError_t>(100000 + (int)rc));
+  return rc == CUDA_SUCCESS;
 }
 
 }  // namespace tc

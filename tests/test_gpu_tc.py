@@ -243,3 +243,31 @@ def test_persistent_backward_is_exact_on_integer_inputs(shape, precision):
     np.testing.assert_array_equal(gb.cpu().numpy().astype(np.float64), wb)
     ga2, gb2 = fn2.correlation_grad(gr.cuda(), a.cuda(), b.cuda(), *ARGS, precision=precision)
     assert torch.equal(ga, ga2) and torch.equal(gb, gb2)
+
+
+def test_first_cuda_action_of_a_fresh_thread_is_one_of_our_launches():
+    """PyTorch's autograd worker may reach our backward as its first CUDA action (smoke() does): the tensor-map
+    encode is a driver call and needs a context bound to that thread (CUDA_ERROR_INVALID_CONTEXT otherwise)."""
+    import threading
+    a, b = corr_inputs(1, 12, 16, 64)
+    ad, bd = a.cuda(), b.cuda()
+    go = grad_like((1, 12, 16, 441)).cuda()
+    img, flo = torch.rand(1, 32, 64, 3).cuda(), (torch.randn(1, 32, 64, 2) * 3).cuda()
+    torch.cuda.synchronize()
+    res = {}
+
+    def work():
+        try:
+            res["grads"] = fn2.correlation_grad(go, ad, bd, 1, 20, 1, 2, 20, precision="tf32x3")
+            res["warp"] = fn2.flow_warp(img, flo)
+            torch.cuda.synchronize()
+        except Exception as exc:  # pragma: no cover
+            res["error"] = exc
+
+    t = threading.Thread(target=work)
+    t.start()
+    t.join()
+    assert "error" not in res, res.get("error")
+    wga, wgb = o.c_correlation_grad(go.cpu().numpy(), a.numpy(), b.numpy(), 1, 20, 1, 2, 20, f64=True)
+    assert_close(res["grads"][0].cpu().numpy(), wga)
+    assert_close(res["grads"][1].cpu().numpy(), wgb)
