@@ -34,6 +34,8 @@ _SIGNATURES = {
     "fn2_correlation_forward": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_forward_fused": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int, ctypes.c_float, c_int, c_void_p,
                                               c_size_t, c_void_p]),
+    "fn2_correlation_backward_fused": (c_int, [c_void_p] * 6 + _CORR_GEOM + [c_int, ctypes.c_float, c_int, c_void_p,
+                                               c_size_t, c_void_p]),
     "fn2_correlation_backward": (c_int, [c_void_p] * 5 + _CORR_GEOM + [c_int, c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_forward_halo": (c_int, [c_void_p] * 3 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),
     "fn2_correlation_backward_halo": (c_int, [c_void_p] * 5 + _CORR_GEOM + [c_int] * 3 + [c_void_p, c_size_t, c_void_p]),

@@ -136,8 +136,9 @@ def correlation(input_a, input_b, kernel_size, max_displacement, stride_1, strid
 class _CorrelationLeakyConcat(torch.autograd.Function):
     """cc_relu = LeakyReLU(correlation(a, b, ...)) written straight into channels [offset, offset + D) of ``buf``.
 
-    Backward: d cc = d buf[..., offset:offset+D] * (cc_relu > 0 ? 1 : slope) (torch elementwise), then the
-    CorrelationGrad kernel; the other channels of d buf pass through to ``buf``'s producer."""
+    Backward: d cc = d buf[..., offset:offset+D] * (cc_relu > 0 ? 1 : slope), formed inside the CorrelationGrad
+    kernel's gradient gather (``fn2_correlation_backward_fused``); the other channels of d buf pass through to
+    ``buf``'s producer."""
 
     @staticmethod
     def forward(ctx, a, b, buf, offset, slope, k, md, s1, s2, pad, prec):
@@ -166,12 +167,24 @@ class _CorrelationLeakyConcat(torch.autograd.Function):
     def backward(ctx, gbuf):
         a, b, buf = ctx.saved_tensors
         offset, oc, slope, k, md, s1, s2, pad, prec = ctx.attrs
-        cc = buf[..., offset:offset + oc]
-        g = (gbuf[..., offset:offset + oc] * torch.where(cc > 0, 1.0, float(slope))).contiguous()
-        ga, gb = correlation_grad(g, a, b, k, md, s1, s2, pad, precision=prec)
-        gbuf = gbuf.clone()
-        gbuf[..., offset:offset + oc] = 0
-        return ga, gb, gbuf, None, None, None, None, None, None, None, None
+        gbuf = gbuf.contiguous()
+        N, H, W, C = a.shape
+        geom = (N, H, W, C, k, md, s1, s2, pad)
+        ga, gb = torch.empty_like(a), torch.empty_like(b)
+        # slice + LeakyReLU derivative inside the CorrelationGrad kernel's gradient gather: no masked copy of the
+        # 441 channels is made (fn2_correlation_backward_fused)
+        with torch.cuda.device(a.device):
+            ws, nbytes, wsp = _workspace(a, geom, prec, 1)
+            st = _lib.lib().fn2_correlation_backward_fused(
+                gbuf.data_ptr() + 4 * offset, buf.data_ptr() + 4 * offset, a.data_ptr(), b.data_ptr(), ga.data_ptr(),
+                gb.data_ptr(), *geom, int(buf.shape[3]), float(slope), prec, wsp, nbytes,
+                _lib.current_stream_ptr(a.device))
+        _lib.check(st, "CorrelationGrad")
+        # what flows on to the buffer's producer: the channels this op did not overwrite (conv_redir's 32)
+        gpass = torch.zeros_like(gbuf)
+        gpass[..., :offset] = gbuf[..., :offset]
+        gpass[..., offset + oc:] = gbuf[..., offset + oc:]
+        return ga, gb, gpass, None, None, None, None, None, None, None, None
 
 
 def correlation_leaky_concat(input_a, input_b, kernel_size, max_displacement, stride_1, stride_2, padding, buf,

@@ -101,7 +101,14 @@ __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const
   const int x = xx + g.pad, y = yy + g.pad;  // padded coordinates
   const float* an = a + (size_t)n * g.H * g.W * g.C;
   const float* bn = b + (size_t)n * g.bH * g.W * g.C;
-  const float* gn = gout + (size_t)n * g.oH * g.oW * g.D;
+  const float* gn = gout + (size_t)n * g.oH * g.oW * g.gPitch;
+  const float* mn = g.gMask ? g.gMask + (size_t)n * g.oH * g.oW * g.gPitch : nullptr;
+  // gradient of output element (y2, x2, op), times the fused LeakyReLU's derivative when a mask is given
+  auto gval = [&](int y2, int x2, int op) {
+    const size_t i = ((size_t)y2 * g.oW + x2) * g.gPitch + op;
+    const float v = __ldg(gn + i);
+    return mn ? (__ldg(mn + i) > 0.f ? v : v * g.slope) : v;
+  };
   const float sumelems = (float)(g.k * g.k * g.C);
 
   // output range covering this element for d/da (same for every displacement)
@@ -123,7 +130,7 @@ __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const
             const float bv = __ldg(bn + ((size_t)yb * g.W + xb) * g.C + c);
             for (int y2 = aymin; y2 <= aymax; ++y2)
               for (int x2 = axmin; x2 <= axmax; ++x2)
-                sa = fmaf(__ldg(gn + ((size_t)y2 * g.oW + x2) * g.D + op), bv, sa);
+                sa = fmaf(gval(y2, x2, op), bv, sa);
           }
         }
         {
@@ -137,7 +144,7 @@ __global__ void __launch_bounds__(256) corr_generic_bwd_kernel(CorrGeom g, const
               const float av = __ldg(an + ((size_t)yq * g.W + xq) * g.C + c);
               for (int y2 = ymin; y2 <= ymax; ++y2)
                 for (int x2 = xmin; x2 <= xmax; ++x2)
-                  sb = fmaf(__ldg(gn + ((size_t)y2 * g.oW + x2) * g.D + op), av, sb);
+                  sb = fmaf(gval(y2, x2, op), av, sb);
             }
           }
         }

@@ -64,6 +64,9 @@ struct BwdParams {
   CUtensorMap x[2][4];  // [mode][class]: mode 0 (da) streams b, mode 1 (db) streams a
   CUtensorMap o[2][4];  // [mode][class]: the output tensor (da, db), boxes of 32 channels x 32 class pixels, no swizzle
   const float* grad;
+  const float* mask;    // FUSED: stored activations, indexed like grad (LeakyReLU derivative = sign test); else unused
+  int gpitch;           // floats between consecutive pixels of grad / mask (D for a plain gradient tensor)
+  float slope;
   float* out[2];        // da, db
   int N, H, W, C, s2, ncls;
   int Hc[2], Wc[2];
@@ -90,7 +93,7 @@ constexpr size_t bwd_smem_bytes() {
   return 1024 + (size_t)NST * (XSTAGE + (X3 ? 2 : 1) * GSTAGE) + sizeof(BwdBarriers<NST>);
 }
 
-template <int NST, int S2, int R, bool X3>
+template <int NST, int S2, int R, bool X3, bool FUSED>
 __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_constant__ BwdParams P) {
   static_assert(NST >= 2 && NST <= 4, "the G builders unroll the stage ring explicitly");
   constexpr int GW = 2 * R + 1;
@@ -236,7 +239,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
     // the thread's 16 elements, and (per 32-column source half hx) the validity mask of the 16 (a-pixel, b-pixel)
     // pairs.  The 16 global addresses of an item are base + rr * (S2*D - 1) floats (next a-pixel, displacement
     // one less), so they are immediates off one 64-bit base pointer.
-    constexpr int ESTRIDE = S2 * D - 1;
+    // (FUSED: the pixel pitch is a run-time value, the gradient being a channel window of the concat buffer)
+    const int GP = FUSED ? P.gpitch : D;
+    const int ESTRIDE = S2 * GP - 1;
     uint32_t saddr[16];
     uint32_t okmask[2] = {0u, 0u};
     const uint32_t sG_q = smem_u32(sG) + (uint32_t)q * GBLOCK;
@@ -258,7 +263,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
       }
     }
     const bool qrow_ok = (r0 + q < Hout);
-    const float* gimg = P.grad + (size_t)n * P.H * P.W * D;
+    const float* gimg = P.grad + (size_t)n * P.H * P.W * GP;
+    const ptrdiff_t moff = FUSED ? (P.mask - P.grad) : 0;   // same indexing, other tensor
 
     // The gather of one item (16 floats per thread, 84-byte runs of `gradients`) is a full L2/DRAM round trip, so
     // items it+1 .. it+NST-1 are fetched into registers before item it is waited for and stored.
@@ -273,10 +279,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) corr_tc_bwd_kernel(const __grid_c
       const uint32_t m = blk_ok ? okmask[hx] : 0u;
       // block rows are a-pixels, block columns are b-pixels; the tile owns the a-columns for da, the b-columns for db
       const int a0 = (mode ? xs0 : x0) + xh, b0 = (mode ? x0 : xs0) + xb;
-      const float* base = gimg + ((ptrdiff_t)((blk_ok ? ya : 0) * S2 + cy) * P.W + cx) * D + (blk_ok ? p + R : 0) * GW +
-                          (ptrdiff_t)a0 * (S2 * D) + (b0 - a0 + R);
+      const float* base = gimg + ((ptrdiff_t)((blk_ok ? ya : 0) * S2 + cy) * P.W + cx) * GP + (blk_ok ? p + R : 0) * GW +
+                          (ptrdiff_t)a0 * (S2 * GP) + (b0 - a0 + R);
 #pragma unroll
       for (int rr = 0; rr < 16; ++rr) v[rr] = ((m >> rr) & 1u) ? __ldg(base + rr * ESTRIDE) : 0.f;
+      if constexpr (FUSED) {   // times the derivative of the LeakyReLU fused into the forward (flownet_c.py:41)
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr)
+          if ((m >> rr) & 1u) v[rr] = __ldg(base + moff + rr * ESTRIDE) > 0.f ? v[rr] : v[rr] * P.slope;
+      }
     };
     {
       float vq[NST][16];   // register ring aligned with the stage ring: item it lives in vq[it % NST]
@@ -402,6 +413,10 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
   const bool x3 = precision == FN2_PREC_TF32X3;
   BwdParams P;
   P.grad = gout;
+  const bool fused = g.gMask != nullptr || g.gPitch != g.D;
+  P.mask = g.gMask ? g.gMask : gout;   // pitch without a mask: slope 1 makes the sign test a no-op
+  P.gpitch = g.gPitch;
+  P.slope = g.gMask ? g.slope : 1.0f;
   P.out[0] = ga; P.out[1] = gb;
   P.N = g.N; P.H = g.H; P.W = g.W; P.C = g.C; P.s2 = g.s2; P.ncls = g.s2 * g.s2;
   P.bH = g.bH; P.boff = g.bTop / g.s2;
@@ -438,23 +453,22 @@ int corr_tc_backward_launch(const CorrGeom& g, const float* gout, const float* a
         return FN2_E_CUDA;
     }
   }
-  auto kern = x3 ? (g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true> : corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true>)
-                 : (g.s2 == 2 ? corr_tc_bwd_kernel<BWD_NST, 2, 10, false> : corr_tc_bwd_kernel<BWD_NST, 1, 10, false>);
+  using Kern = void (*)(const BwdParams);
+  const Kern table[2][2][2] = {   // [x3][s2 == 2][fused]
+      {{corr_tc_bwd_kernel<BWD_NST, 1, 10, false, false>, corr_tc_bwd_kernel<BWD_NST, 1, 10, false, true>},
+       {corr_tc_bwd_kernel<BWD_NST, 2, 10, false, false>, corr_tc_bwd_kernel<BWD_NST, 2, 10, false, true>}},
+      {{corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true, false>, corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true, true>},
+       {corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true, false>, corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true, true>}}};
+  const Kern kern = table[x3 ? 1 : 0][g.s2 == 2 ? 1 : 0][fused ? 1 : 0];
   const size_t smem = x3 ? bwd_smem_bytes<BWD_NST_X3, true>() : bwd_smem_bytes<BWD_NST, false>();
   static PerDeviceOnce once;   // function attributes are per device
-  const cudaError_t attr_err = per_device_once(once, [] {
-    cudaError_t e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 2, 10, false>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)bwd_smem_bytes<BWD_NST, false>());
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST, 1, 10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)bwd_smem_bytes<BWD_NST, false>());
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST_X3, 2, 10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)bwd_smem_bytes<BWD_NST_X3, true>());
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(corr_tc_bwd_kernel<BWD_NST_X3, 1, 10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               (int)bwd_smem_bytes<BWD_NST_X3, true>());
+  const cudaError_t attr_err = per_device_once(once, [&table] {
+    cudaError_t e = cudaSuccess;
+    for (int x = 0; x < 2 && e == cudaSuccess; ++x)
+      for (int q = 0; q < 2 && e == cudaSuccess; ++q)
+        for (int f = 0; f < 2 && e == cudaSuccess; ++f)
+          e = cudaFuncSetAttribute(table[x][q][f], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)(x ? bwd_smem_bytes<BWD_NST_X3, true>() : bwd_smem_bytes<BWD_NST, false>()));
     return e;
   });
   if (attr_err != cudaSuccess) { note_cuda_error(attr_err); (void)cudaGetLastError(); return FN2_E_CUDA; }

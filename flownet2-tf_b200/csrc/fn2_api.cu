@@ -75,6 +75,8 @@ static int make_geom(int N, int H, int W, int C, int k, int md, int s1, int s2, 
   g->bTop = 0;
   g->oPitch = g->D;
   g->slope = 1.0f;
+  g->gPitch = g->D;
+  g->gMask = nullptr;
   return FN2_OK;
 }
 
@@ -180,6 +182,23 @@ int fn2_correlation_forward_fused(const float* a, const float* b, float* out, in
   return correlation_forward(g, a, b, out, precision, ws, ws_bytes, stream);
 }
 
+int fn2_correlation_backward_fused(const float* gout, const float* activations, const float* a, const float* b, float* ga,
+                                   float* gb, int N, int H, int W, int C, int k, int md, int s1, int s2, int pad,
+                                   int pixel_pitch, float leaky_slope, int precision, void* ws, size_t ws_bytes,
+                                   void* stream) {
+  CorrGeom g;
+  const int rc = make_geom(N, H, W, C, k, md, s1, s2, pad, &g);
+  if (rc != FN2_OK) return rc;
+  if (pixel_pitch < g.D) return FN2_E_BAD_SHAPE;
+  if (!(leaky_slope > 0.f)) return FN2_E_BAD_PARAM;   // the mask is the sign of the stored activation
+  if (!activations) return FN2_E_BAD_POINTER;
+  g.gPitch = pixel_pitch;
+  g.gMask = activations;
+  g.slope = leaky_slope;
+  // a channel window of a wider tensor starts at an arbitrary channel: 4-byte alignment is all these two need
+  return correlation_backward(g, gout, a, b, ga, gb, precision, ws, ws_bytes, stream);
+}
+
 int fn2_correlation_forward_halo(const float* a, const float* b, float* out, int N, int H, int W, int C, int k, int md,
                                  int s1, int s2, int pad, int halo_top, int halo_bottom, int precision, void* ws,
                                  size_t ws_bytes, void* stream) {
@@ -229,7 +248,9 @@ int fn2_correlation_backward(const float* gout, const float* a, const float* b, 
 static int correlation_backward(const CorrGeom& g, const float* gout, const float* a, const float* b, float* ga,
                                 float* gb, int precision, void* ws, size_t ws_bytes, void* stream) {
   if (!gout || !a || !b || !ga || !gb) return FN2_E_BAD_POINTER;
-  if (!aligned16(gout) || !aligned16(a) || !aligned16(b) || !aligned16(ga) || !aligned16(gb)) return FN2_E_BAD_POINTER;
+  if (!aligned16(a) || !aligned16(b) || !aligned16(ga) || !aligned16(gb)) return FN2_E_BAD_POINTER;
+  if (g.gMask ? ((reinterpret_cast<uintptr_t>(gout) | reinterpret_cast<uintptr_t>(g.gMask)) & 3u) != 0 : !aligned16(gout))
+    return FN2_E_BAD_POINTER;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   switch (precision) {
     case FN2_PREC_FP32:

@@ -26,6 +26,12 @@ struct CorrGeom {
   // non-positive values (1 = none).
   int oPitch;
   float slope;
+  // Fused backward (fn2_correlation_backward_fused): `gradients` is a channel window of a wider tensor with gPitch
+  // floats between consecutive pixels (D for a plain [N,oH,oW,D] tensor) and, when gMask is set, every gradient is
+  // multiplied by the derivative of the fused LeakyReLU, read off the sign of the stored activation at the same
+  // index of gMask (same pitch): 1 where it is > 0, `slope` elsewhere (flownet_c.py:41-46 backwards).
+  int gPitch;
+  const float* gMask;
 };
 
 // Records a launch for fn2_launch_count() and returns the status of the launch that was just made.

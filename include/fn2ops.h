@@ -108,6 +108,20 @@ FN2_API int fn2_correlation_forward_fused(const float* input_a, const float* inp
                                   int out_pixel_pitch, float leaky_slope, int precision, void* workspace,
                                   size_t workspace_bytes, void* stream);
 
+/* The backward of fn2_correlation_forward_fused, with the two steps that precede CorrelationGrad in the reference's
+ * gradient graph fused into the kernel's gradient gather:
+ *   d cc_relu = slice(d net, channels [offset, offset + D))                  gradient of tf.concat, flownet_c.py:44-46
+ *   d cc      = d cc_relu * (cc_relu > 0 ? 1 : leaky_slope)                  gradient of LeakyReLU,  flownet_c.py:41
+ * `gradients` points at the first correlation channel of pixel (0,0,0) inside the gradient of the concat buffer,
+ * `activations` at the same place inside the buffer the forward wrote (the mask is the sign of the stored value, which
+ * needs leaky_slope > 0); both have `pixel_pitch` floats per pixel and only need 4-byte alignment.  No masked
+ * 441-channel copy is materialised.  With pixel_pitch == D and leaky_slope == 1 this is fn2_correlation_backward. */
+FN2_API int fn2_correlation_backward_fused(const float* gradients, const float* activations, const float* input_a,
+                                   const float* input_b, float* backprops_a, float* backprops_b, int N, int H, int W,
+                                   int C, int kernel_size, int max_displacement, int stride_1, int stride_2, int pad,
+                                   int pixel_pitch, float leaky_slope, int precision, void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
 /* Replaces REGISTER_OP("CorrelationGrad") + CorrelationGradKernel<GPUDevice>::Compute
  * (correlation_op.cc:64-82, correlation_grad_kernel.cc:15-159) and CorrelationGradA/B
  * (correlation_grad_kernel.cu.cc:191-259).  One launch set for the whole batch; no atomics; both gradients

@@ -43,25 +43,46 @@ def test_fused_matches_oracle_fp32():
     assert_close(buf[..., 32:].cpu().numpy(), want, rel=1e-5, abs_=1e-6, what="fused fp32")
 
 
-def test_fused_backward_equals_unfused_backward():
-    a0, b0 = corr_inputs(2, 24, 32, 128)
+@pytest.mark.parametrize("precision,shape", [("tf32", (2, 24, 32, 128)), ("tf32x3", (2, 24, 32, 128)),
+                                             ("tf32x3", (1, 13, 70, 64)), ("fp32", (1, 10, 12, 32))])
+def test_fused_backward_equals_unfused_backward(precision, shape):
+    """fn2_correlation_backward_fused (concat slice + LeakyReLU derivative inside the CorrelationGrad kernel's gradient
+    gather) against the three separate graph nodes: the same products in the same order, so bit-equal."""
+    N, H, W, C = shape
+    a0, b0 = corr_inputs(N, H, W, C)
     a0 = a0 - 0.3
-    g = torch.randn(2, 24, 32, 473, generator=torch.Generator().manual_seed(3)).cuda()
+    g = torch.randn(N, H, W, 473, generator=torch.Generator().manual_seed(3)).cuda()
     res = []
     for fused in (True, False):
         a, b = a0.cuda().requires_grad_(), b0.cuda().requires_grad_()
-        redir = torch.randn(2, 24, 32, 32, generator=torch.Generator().manual_seed(4)).cuda().requires_grad_()
+        redir = torch.randn(N, H, W, 32, generator=torch.Generator().manual_seed(4)).cuda().requires_grad_()
         if fused:
-            buf = torch.empty(2, 24, 32, 473, device="cuda")
+            buf = torch.empty(N, H, W, 473, device="cuda")
             buf[..., :32] = redir
-            net = fn2.correlation_leaky_concat(a, b, *ARGS, buf, 32, 0.1, precision="tf32")
+            net = fn2.correlation_leaky_concat(a, b, *ARGS, buf, 32, 0.1, precision=precision)
         else:
-            cc = torch.nn.functional.leaky_relu(fn2.correlation(a, b, *ARGS, precision="tf32"), 0.1)
+            cc = torch.nn.functional.leaky_relu(fn2.correlation(a, b, *ARGS, precision=precision), 0.1)
             net = torch.cat([redir, cc], dim=3)
         (net * g).sum().backward()
         res.append((a.grad.clone(), b.grad.clone(), redir.grad.clone()))
     for x, y in zip(*res):
         assert torch.equal(x, y)
+
+
+def test_fused_backward_matches_oracle():
+    """The fused backward against the float64 oracle of CorrelationGrad fed with the masked, sliced gradient."""
+    a, b = corr_inputs(1, 12, 16, 64)
+    a = a - 0.2
+    buf = torch.zeros(1, 12, 16, 473, device="cuda")
+    ad, bd = a.cuda().requires_grad_(), b.cuda().requires_grad_()
+    net = fn2.correlation_leaky_concat(ad, bd, *ARGS, buf, 32, 0.1, precision="tf32x3")
+    g = torch.randn(1, 12, 16, 473, generator=torch.Generator().manual_seed(5))
+    (net * g.cuda()).sum().backward()
+    cc = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
+    gm = (g[..., 32:].numpy() * np.where(cc > 0, 1.0, 0.1)).astype(np.float32)
+    wga, wgb = o.c_correlation_grad(gm, a.numpy(), b.numpy(), *ARGS, f64=True)
+    assert_close(ad.grad.cpu().numpy(), wga, what="fused backprops_a")
+    assert_close(bd.grad.cpu().numpy(), wgb, what="fused backprops_b")
 
 
 def test_fused_errors():
