@@ -8,7 +8,7 @@ One *step* = one pass of the hot path over one batch of B synthetic 512x384 imag
 metric = image pairs / s (whole job, all GPUs; batch-sharded, no collective on the data path => weak scaling).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision auto|fp32|tf32x3|tf32]
-                    [--config hotpath|strips4k]
+                    [--config hotpath|strips4k|flownetc_train|flownet2_infer]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus N --steps K --warmup W
 
@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default=os.environ.get("FN2_BENCH_PRECISION", "auto"))
-    ap.add_argument("--config", default="hotpath", choices=["hotpath", "strips4k"])
+    ap.add_argument("--config", default="hotpath", choices=["hotpath", "strips4k", "flownetc_train", "flownet2_infer"])
     ap.add_argument("--eager", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--batch", type=int, default=32, help="image pairs per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -86,13 +86,17 @@ def executed_mma_flops(batch, precision, hc=HC, wc=WC):
     hcl, wcl = (hc + 1) // 2, (wc + 1) // 2
     tx = (wcl + 31) // 32
     nhx = 2 if tx > 1 else 1
-    rows_f = 8 if (precision == "tf32" and tx == 1) else (4 if precision == "tf32" else 2)
+    # forward tilings: tf32 narrow = CTA pair, 8 a-rows, blocks of 4 b-rows (M256 N128); tf32 wide = 4 a-rows (M128
+    # N128); tf32x3 narrow = CTA pair, 4 a-rows, blocks of 4 b-rows with the hi/lo split folded in (M256 N256);
+    # tf32x3 wide = 2 a-rows, blocks of 2 b-rows (M128 N128)
+    if precision == "tf32":
+        rows_f, brows, m, n = (8, 4, 256, 128) if tx == 1 else (4, 4, 128, 128)
+    else:
+        rows_f, brows, m, n = (4, 4, 256, 256) if tx == 1 else (2, 2, 128, 128)
     fwd = 0.0
     for y0 in range(0, hcl, rows_f):
         lo, hi = max(0, y0 - 10), min(hcl - 1, y0 + rows_f - 1 + 10)
-        blocks = (hi - lo + 1 + 3) // 4 * nhx
-        m = {8: 256, 4: 128, 2: 128}[rows_f]
-        n = 256 if precision == "tf32x3" else 128
+        blocks = (hi - lo + brows) // brows * nhx
         fwd += blocks * 2.0 * m * n * CC
     bwd = 0.0
     for r0 in range(0, hcl, 8):
@@ -339,18 +343,46 @@ def strips_bench(torch, dist, fn2, dev, rank, world, precision, steps, warm, hbm
         t = torch.tensor([e0.elapsed_time(e1) / 20], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         comm_ms = float(t.item())
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sync()
-    e0.record()
-    for _ in range(steps):
-        step()
-    e1.record()
-    sync()
-    ms = e0.elapsed_time(e1) / steps
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    def timed_steps(fn):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync()
+        ms_ = e0.elapsed_time(e1) / steps
+        if world > 1:
+            t_ = torch.tensor([ms_], device=dev)
+            dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+            ms_ = float(t_.item())
+        return ms_
+
+    eager_ms = timed_steps(step)
+    # The whole step -- kernels, the two ncclSend/Recv exchanges, the adds -- captured in ONE CUDA graph: every call only
+    # enqueues work, so the step replays without Python between its ~12 launches (at 4K the eager step is bound by the
+    # host: ~0.9 ms of launch calls for ~0.3 ms of device work per rank).  Every rank decides the same way.
+    graph_ms, graph_note = None, None
+    if os.environ.get("FN2_STRIPS_GRAPH", "1") != "0":
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    step()
+                a.grad = None
+                b.grad = None
+                gr = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gr, stream=side):
+                    step()
+                for _ in range(3):
+                    gr.replay()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            sync()
+            graph_ms = timed_steps(gr.replay)
+        except Exception as exc:  # pragma: no cover
+            graph_note = "capture failed: %s" % str(exc)[:160]
+    ms = graph_ms if graph_ms is not None else eager_ms
     ab, fl = algorithmic_bytes(1, H4K, W4K), corr_flops(1, H4K, W4K)
     nbytes = ab["corr_fwd"] + ab["corr_bwd"]
     return {
@@ -365,8 +397,80 @@ def strips_bench(torch, dist, fn2, dev, rank, world, precision, steps, warm, hbm
                     "boundary in forward, 20 rows of backprops_b partial sums in backward",
             "bytes_per_direction_per_boundary": 20 * W4K * CC * 4, "comm_nranks": world,
             "exchange_alone_ms": round(comm_ms, 4), "overlapped_with": "interior rows of the strip"},
-        "launch": "eager autograd calls (correlation_strips forward + backward)",
+        "launch": "one CUDA graph per step (kernels + NCCL send/recv captured)" if graph_ms is not None
+                  else "eager autograd calls (correlation_strips forward + backward)",
+        "ms_per_step_eager": round(eager_ms, 4), "graph_note": graph_note,
     }
+
+
+# ------------------------------------------------------------------------- caller graphs (configs 3 and 4)
+def graphs_bench(torch, dist, dev, rank, world, precision, config, steps, warm, batch):
+    """BASELINE configs 3 and 4, end to end through flownet2_tf_b200.graphs (the three ops are this library's kernels,
+    the convolutions are cuDNN library calls on channels_last tensors, TF32 allowed as torch's default):
+      flownetc_train : FlowNetC forward + multi-scale loss + backward + Adam step, `batch` 512x384 pairs per GPU,
+                       random-init weights, synthetic pairs; N > 1 = DistributedDataParallel (NCCL gradient all-reduce)
+      flownet2_infer : FlowNet2 (CSS + SD + fusion) stacked inference, `batch` pairs per GPU, no gradients."""
+    from flownet2_tf_b200 import graphs as G
+    torch.manual_seed(1234)
+    gen = torch.Generator(device=dev).manual_seed(99 + rank)
+    inputs = {"input_a": torch.rand(batch, HI, WI, 3, device=dev, generator=gen),
+              "input_b": torch.rand(batch, HI, WI, 3, device=dev, generator=gen)}
+    if config == "flownetc_train":
+        net = G.FlowNetC(precision=precision).to(dev)
+        ops = net.ops
+        model = net
+        if world > 1:
+            model = torch.nn.parallel.DistributedDataParallel(net, device_ids=[dev.index], gradient_as_bucket_view=True)
+        opt = torch.optim.Adam(net.parameters(), lr=1e-4)     # training_schedules.py: Adam, 1e-4
+        gt = torch.randn(batch, HI, WI, 2, device=dev, generator=gen) * 5
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            out = model(inputs)
+            loss, _ = G.multiscale_loss(gt, out, ops)
+            loss = loss + G.l2_regularization(net, 4e-4)      # flownet_c.py:27: weight decay 0.0004
+            loss.backward()
+            opt.step()
+            return loss
+        what = "FlowNetC forward + multi-scale EPE loss + backward + Adam step"
+    else:
+        net = G.FlowNet2(precision=precision).to(dev).eval()
+
+        def step():
+            with torch.no_grad():
+                return net(inputs)["flow"]
+        what = "FlowNet2 (CSS + SD + fusion) stacked inference"
+
+    def sync():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(warm, 3)):
+        step()
+    sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        res = step()
+    e1.record()
+    sync()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ok = bool(torch.isfinite(res.detach() if hasattr(res, "detach") else res).all())
+    return {"metric": "image_pairs_per_s", "value": world * batch / (ms * 1e-3), "unit": "pairs/s", "n_gpus": world,
+            "steps": steps, "warmup": max(warm, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": precision, "data": "synthetic",
+            "config": {"workload": "%s, %d synthetic 512x384 pairs per GPU, random-init weights" % (what, batch),
+                       "pairs_per_gpu": batch,
+                       "parallelism": ("DistributedDataParallel, NCCL gradient all-reduce over %d ranks" % world)
+                       if (config == "flownetc_train" and world > 1) else "batch-sharded replicas",
+                       "convolutions": "cuDNN (library), channels_last, TF32 allowed; correlation / flow_warp / "
+                                       "downsample: this library's kernels, correlation precision %s" % precision},
+            "finite": ok, "launch": "eager PyTorch"}
 
 
 # ------------------------------------------------------------------------------------------------------ ours
@@ -416,6 +520,15 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.config in ("flownetc_train", "flownet2_infer"):
+        gb = args.batch if args.batch != 32 or args.config == "flownetc_train" else 8   # cfg4: 64 pairs over 8 GPUs
+        line = graphs_bench(torch, dist, dev, rank, world, precision, args.config, args.steps, args.warmup, gb)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     if args.config == "strips4k":
         res = strips_bench(torch, dist, fn2, dev, rank, world, precision, args.steps, args.warmup, hbm_peak)
@@ -725,6 +838,24 @@ def main():
             cfg2[name] = op_entry(ms, ab8[name], hbm_peak)
         cfg2["pairs_per_s"] = round(8e3 / sum(cfg2[n]["ms"] for n in ("warp_fwd", "warp_bwd", "downsample")), 1)
         del IMG, FLO, GI
+        # ---- the same two flow_warp kernels on the reference's REAL flow (data/samples/0flow.flo as packed in
+        # tests/golden/sample0.npz): smooth, mean 2 px, down to -109 px -- the other regime from the iid N(0, 8 px) ----
+        fix = os.path.join(ROOT, "tests", "golden", "sample0.npz")
+        if os.path.exists(fix):
+            import numpy as np
+            z = np.load(fix)
+            img1 = torch.from_numpy(z["image"].astype(np.float32)).to(dev)
+            flo1 = torch.from_numpy(z["flow"]).to(dev)
+            IMG = [torch.stack([img1.roll(7 * (i * B + j), 0) for j in range(B)]).contiguous() for i in range(2)]
+            FLO = [torch.stack([flo1.roll(7 * (i * B + j), 0) for j in range(B)]).contiguous() for i in range(2)]
+            GI = [torch.randn(B, HI, WI, 3, device=dev, generator=gen) for _ in range(2)]
+            cfg2["on_the_reference_sample_flow"] = {
+                "workload": "batch %d of data/samples pair 0 (rows rolled per image), real ground-truth flow" % B,
+                "warp_fwd": op_entry(graph_time(torch, [(lambda i=i: fn2.flow_warp(IMG[i], FLO[i])) for i in range(2)],
+                                                5, tstream), abytes["warp_fwd"], hbm_peak),
+                "warp_bwd": op_entry(graph_time(torch, [(lambda i=i: fn2.flow_warp_grad(IMG[i], FLO[i], GI[i]))
+                                                        for i in range(2)], 5, tstream), abytes["warp_bwd"], hbm_peak)}
+            del IMG, FLO, GI
 
     # ---- the reference's own CUDA kernels on this GPU, per op (they are the reference's only implementation) ----
     ref_gpu = None

@@ -56,6 +56,7 @@ constexpr int STG_FLOATS = 32 * 33;     // transposed staging tile [b column][a 
 struct X3Params {
   CUtensorMap a[4];   // per parity class, boxes of 2 rows x 32 cols x 32 channels
   CUtensorMap b[4];   // per parity class, boxes of 2 rows x 32 cols x 32 channels
+  CUtensorMap bw[4];  // per parity class, boxes of 1 row x 64 cols x 32 channels (CTA-pair kernel, wide images)
   float* out;
   int N, H, W, C, D, s2, ncls;
   int Hc[2], Wc[2];   // class-space extent per parity
@@ -383,30 +384,36 @@ struct __align__(8) X3PairBarriers {
 };
 
 struct X3Work {
-  int n, cls, cy, cx, Hc, Wc, Hcb, y0p, s_first, nblk;
+  int n, cls, cy, cx, Hc, Wc, Hcb, y0p, x0, s_first, nblk;
   bool valid;
 };
-template <int R>
+template <int R, bool WIDE>
 __device__ __forceinline__ X3Work x3_work(const X3Params& P, int w) {
   X3Work k;
   int t = w;
+  const int tx = t % P.TX; t /= P.TX;
   const int typ = t % P.TYP; t /= P.TYP;
   k.cls = t % P.ncls;
   k.n = t / P.ncls;
   k.cy = k.cls / P.s2; k.cx = k.cls % P.s2;
   k.Hc = P.Hc[k.cy]; k.Wc = P.Wc[k.cx]; k.Hcb = P.Hcb[k.cy];
   k.y0p = typ * 2 * PR;
+  k.x0 = tx * TILE_C;
   k.nblk = 0; k.s_first = 0;
-  k.valid = !(k.y0p >= k.Hc || k.Wc < 1);
+  k.valid = !(k.y0p >= k.Hc || k.x0 >= k.Wc);
   if (!k.valid) return k;
   const int ylast = min(k.y0p + 2 * PR - 1, k.Hc - 1);
   k.s_first = max(0, k.y0p + P.boff - R);
   const int s_last = min(k.Hcb - 1, ylast + P.boff + R);
-  k.nblk = max(0, (s_last - k.s_first + PBROWS) / PBROWS);
+  constexpr int RB = WIDE ? 2 : PBROWS;               // b-rows per block
+  k.nblk = max(0, (s_last - k.s_first + RB) / RB);
   return k;
 }
 
-template <int R>
+// WIDE (class width > 32): a block is TWO b-rows of 64 columns [x0 - 16, x0 + 48) -- one row per CTA -- so that the
+// +-10 window of every pixel of the 32-column a tile lies inside one block row; columns outside the image are TMA zero
+// fill (the op's padding), so no displacement needs a lateral test.
+template <int R, bool WIDE>
 __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const __grid_constant__ X3Params P) {
   constexpr int GW = 2 * R + 1;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -451,24 +458,28 @@ __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const
     if (elect_one()) {
       int it = 0, used = 0;
       for (int w = pair0; w < P.nwork; w += npairs) {
-        const X3Work k = x3_work<R>(P, w);
+        const X3Work k = x3_work<R, WIDE>(P, w);
         if (k.nblk == 0) continue;
         const int y0 = k.y0p + (int)rank * PR;
         const int ya = y0 < k.Hc ? y0 : 0;   // a phantom second tile (odd number of row tiles) loads valid rows, unused
         for (int blk = 0; blk < k.nblk; ++blk) {
-          const int srow = k.s_first + blk * PBROWS + BROWS * (int)rank;   // this CTA's two b-rows of the block
+          // this CTA's part of the block: two b-rows of 32 columns, or (WIDE) one b-row of 64 columns
+          const int srow = WIDE ? k.s_first + blk * 2 + (int)rank : k.s_first + blk * PBROWS + BROWS * (int)rank;
           for (int kc = 0; kc < nkc; ++kc, ++it) {
             if (blk == 0) {   // the a tile goes out chunk by chunk, interleaved with block 0 which consumes it in this order
               if (used > 0) mbar_wait(smem_u32(&bars->a_free[kc]), (used - 1) & 1);   // the previous tile is done with it
               const uint32_t a_full = smem_u32(&bars->a_full[kc]);
               mbar_expect_tx(a_full, A_HALF);
-              tma_load_4d(smem_u32(sA + (size_t)kc * A_CHUNK), &P.a[k.cls], a_full, kc * KCH, 0, ya, k.n);
+              tma_load_4d(smem_u32(sA + (size_t)kc * A_CHUNK), &P.a[k.cls], a_full, kc * KCH, k.x0, ya, k.n);
             }
             const int stage = it % NSTAGE;
             mbar_wait(smem_u32(&bars->empty[stage]), ((it / NSTAGE) & 1) ^ 1);
             const uint32_t full = smem_u32(&bars->full[stage]);
             mbar_expect_tx(full, B_HALF);
-            tma_load_4d(smem_u32(sB + (size_t)stage * B_STAGE), &P.b[k.cls], full, kc * KCH, 0, srow, k.n);
+            if (WIDE)
+              tma_load_4d(smem_u32(sB + (size_t)stage * B_STAGE), &P.bw[k.cls], full, kc * KCH, k.x0 - 16, srow, k.n);
+            else
+              tma_load_4d(smem_u32(sB + (size_t)stage * B_STAGE), &P.b[k.cls], full, kc * KCH, 0, srow, k.n);
           }
         }
         ++used;
@@ -480,7 +491,7 @@ __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const
       constexpr uint32_t idesc = idesc_tf32(256, PBUF_COLS);
       int it = 0, gb = 0, used = 0;
       for (int w = pair0; w < P.nwork; w += npairs) {
-        const X3Work k = x3_work<R>(P, w);
+        const X3Work k = x3_work<R, WIDE>(P, w);
         if (k.nblk == 0) continue;
         for (int blk = 0; blk < k.nblk; ++blk, ++gb) {
           const int buf = gb % PNBUF;
@@ -527,13 +538,13 @@ __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const
     // when that column is outside the class row).  Recomputed per store: a table of GW registers costs more here.
     int gb = 0;
     for (int w = pair0; w < P.nwork; w += npairs) {
-      const X3Work k = x3_work<R>(P, w);
+      const X3Work k = x3_work<R, WIDE>(P, w);
       if (!k.valid) continue;
       const int y = k.y0p + (int)rank * PR + ar;
       const bool row_ok = y < k.Hc;
       const int Y = y * P.s2 + k.cy;
-      const int ncol = min(TILE_C, k.Wc);
-      float* orow0 = P.out + (((size_t)k.n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)k.cx) * P.opitch;
+      const int ncol = min(TILE_C, k.Wc - k.x0);
+      float* orow0 = P.out + (((size_t)k.n * P.H + (row_ok ? Y : 0)) * P.W + (size_t)(k.x0 * P.s2 + k.cx)) * P.opitch;
 
       if (row_ok) {   // displacement rows that point outside the image: zeros, never computed
         const int yb = y + P.boff;
@@ -550,51 +561,103 @@ __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const
         const int buf = gb % PNBUF;
         mbar_wait(smem_u32(&bars->tmem_full[buf]), (gb / PNBUF) & 1);
         tc_fence_after();
-        const int sbase = k.s_first + blk * PBROWS + BROWS * half;
-        const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * PBUF_COLS + half * 128);
-        {
-          const int brMine = isLo, brTheirs = isLo ^ 1;
-          const int sM = sbase + brMine, sT = sbase + brTheirs;
-          const int pM = sM - (y + P.boff), pT = sT - (y + P.boff);
-          const bool okM = row_ok && pM >= -R && pM <= R && sM < k.Hcb;   // the same in both warps of the pair
-          const bool okT = row_ok && pT >= -R && pT <= R && sT < k.Hcb;
+        if constexpr (WIDE) {
+          // this (a-row, half) pair of warps finishes b-row s of the block: 64 columns, tile 0 = columns 0..31 (the lo
+          // warp's partial lands there first), tile 1 = columns 32..63 (the hi warp's)
+          const int sR = k.s_first + blk * 2 + half;
+          const int pR = sR - (y + P.boff);
+          const bool ok = row_ok && pR >= -R && pR <= R && sR < k.Hcb;       // the same in both warps of the pair
+          const uint32_t tb = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * PBUF_COLS + half * 128);
+          float* t0 = sStage + (grp * 2) * STG_FLOATS;
+          float* t1 = t0 + STG_FLOATS;
           float vm[32];
-          if (okT) {   // the partner finishes this b-row: hand it this warp's partial sum
+          if (ok) {
             float v[32];
-            tmem_ld32_sum2(tbase + (uint32_t)(brTheirs * 32), v);
+            tmem_ld32_sum2(tb + (isLo ? 0u : 32u), v);                       // the half the PARTNER completes
+            float* dst = isLo ? t0 : t1;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) theirs[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+            for (int j = 0; j < 32; ++j) dst[j * 33 + lane] = v[j];
+            tmem_ld32_sum2(tb + (isLo ? 32u : 0u), vm);                      // the half this warp completes
           }
-          if (okM) tmem_ld32_sum2(tbase + (uint32_t)(brMine * 32), vm);
-          named_bar_sync(1 + grp, 64);     // both partial sums are in the tiles
-          if (okM) {
+          named_bar_sync(1 + grp, 64);
+          if (ok) {
+            float* own = isLo ? t1 : t0;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) mine[j * 33 + lane] += vm[j];   // same lane, same word the partner wrote
-            __syncwarp();
-            float* orow = orow0 + (pM + R) * GW;
-            // loads in batches of 7 ahead of their stores: a load -> scale -> store chain per value left the warp
-            // waiting on shared-memory latency 21 times per row (48 % of the epilogue's stall samples)
+            for (int j = 0; j < 32; ++j) own[j * 33 + lane] += vm[j];
+          }
+          named_bar_sync(1 + grp, 64);       // both tiles hold the complete sums
+          if (ok) {
+            // each warp stores 16 of the 32 pixel columns: 16 x GW values, coalesced
+            float* orow = orow0 + (pR + R) * GW;
+            const int c16 = isLo * 16;
+            constexpr int NE = 16 * GW;
 #pragma unroll
-            for (int t0 = 0; t0 < GW; t0 += 7) {
-              float xv[7];
+            for (int t0i = 0; t0i < (NE + 31) / 32; t0i += 4) {
+              float xv[4];
 #pragma unroll
-              for (int u = 0; u < 7; ++u) {
-                const int e = (t0 + u) * 32 + lane;
-                const int cc = e / GW, xb = cc + (e - cc * GW) - R;
-                xv[u] = mine[(xb & 31) * 33 + cc];
+              for (int u = 0; u < 4; ++u) {
+                const int e = min((t0i + u) * 32 + lane, NE - 1);
+                const int cc = c16 + e / GW, xb = cc + (e - (e / GW) * GW) - R + 16;
+                xv[u] = t0[(xb >> 5) * STG_FLOATS + (xb & 31) * 33 + cc];
               }
 #pragma unroll
-              for (int u = 0; u < 7; ++u) {
-                const int e = (t0 + u) * 32 + lane;
-                const int cc = e / GW, o = e - cc * GW;
-                const int xb = cc + o - R;
-                float x = (xb >= 0 && xb < 32) ? xv[u] * inv : 0.f;
+              for (int u = 0; u < 4; ++u) {
+                const int e = (t0i + u) * 32 + lane;
+                const int cc = c16 + e / GW, o = e - (e / GW) * GW;
+                float x = xv[u] * inv;
                 x = x > 0.f ? x : x * P.slope;
-                if (cc < ncol) orow[cc * pixstride + o] = x;
+                if (e < NE && cc < ncol) orow[cc * pixstride + o] = x;
               }
             }
           }
-          named_bar_sync(1 + grp, 64);     // the tiles may be overwritten
+          named_bar_sync(1 + grp, 64);       // the tiles may be overwritten
+        } else {
+        const int sbase = k.s_first + blk * PBROWS + BROWS * half;
+          const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * PBUF_COLS + half * 128);
+          {
+            const int brMine = isLo, brTheirs = isLo ^ 1;
+            const int sM = sbase + brMine, sT = sbase + brTheirs;
+            const int pM = sM - (y + P.boff), pT = sT - (y + P.boff);
+            const bool okM = row_ok && pM >= -R && pM <= R && sM < k.Hcb;   // the same in both warps of the pair
+            const bool okT = row_ok && pT >= -R && pT <= R && sT < k.Hcb;
+            float vm[32];
+            if (okT) {   // the partner finishes this b-row: hand it this warp's partial sum
+              float v[32];
+              tmem_ld32_sum2(tbase + (uint32_t)(brTheirs * 32), v);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) theirs[j * 33 + lane] = v[j];   // [b column][a column], conflict-free
+            }
+            if (okM) tmem_ld32_sum2(tbase + (uint32_t)(brMine * 32), vm);
+            named_bar_sync(1 + grp, 64);     // both partial sums are in the tiles
+            if (okM) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) mine[j * 33 + lane] += vm[j];   // same lane, same word the partner wrote
+              __syncwarp();
+              float* orow = orow0 + (pM + R) * GW;
+              // loads in batches of 7 ahead of their stores: a load -> scale -> store chain per value left the warp
+              // waiting on shared-memory latency 21 times per row (48 % of the epilogue's stall samples)
+#pragma unroll
+              for (int t0 = 0; t0 < GW; t0 += 7) {
+                float xv[7];
+#pragma unroll
+                for (int u = 0; u < 7; ++u) {
+                  const int e = (t0 + u) * 32 + lane;
+                  const int cc = e / GW, xb = cc + (e - cc * GW) - R;
+                  xv[u] = mine[(xb & 31) * 33 + cc];
+                }
+#pragma unroll
+                for (int u = 0; u < 7; ++u) {
+                  const int e = (t0 + u) * 32 + lane;
+                  const int cc = e / GW, o = e - cc * GW;
+                  const int xb = cc + o - R;
+                  float x = (xb >= 0 && xb < 32) ? xv[u] * inv : 0.f;
+                  x = x > 0.f ? x : x * P.slope;
+                  if (cc < ncol) orow[cc * pixstride + o] = x;
+                }
+              }
+            }
+            named_bar_sync(1 + grp, 64);     // the tiles may be overwritten
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -609,7 +672,7 @@ __global__ void __launch_bounds__(PNTHREADS, 1) corr_tc_fwd_x3_pair_kernel(const
     const uint32_t conv0 = mapa_u32(smem_u32(&bars->conv[0]), 0);
     int it = 0, used = 0;
     for (int w = pair0; w < P.nwork; w += npairs) {
-      const X3Work k = x3_work<R>(P, w);
+      const X3Work k = x3_work<R, WIDE>(P, w);
       if (k.nblk == 0) continue;
       for (int blk = 0; blk < k.nblk; ++blk) {
         for (int kc = 0; kc < nkc; ++kc, ++it) {
@@ -686,14 +749,15 @@ int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float*
   for (int cls = 0; cls < P.ncls; ++cls) {
     const int cy = cls / g.s2, cx = cls % g.s2;
     if (P.Hc[cy] < 1 || P.Wc[cx] < 1) {  // empty class (H or W == 1 with s2 == 2): map class 0 instead, never used
-      P.a[cls] = P.a[0]; P.b[cls] = P.b[0];
+      P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; P.bw[cls] = P.bw[0];
       continue;
     }
     if (!make_class_map(&P.a[cls], a, g.N, g.H, g.W, g.C, g.s2, cy, cx, P.Hc[cy], P.Wc[cx], TILE_C, XR) ||
-        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, BROWS))
+        !make_class_map(&P.b[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], TILE_C, BROWS) ||
+        !make_class_map(&P.bw[cls], b, g.N, g.bH, g.W, g.C, g.s2, cy, cx, P.Hcb[cy], P.Wc[cx], 2 * TILE_C, 1))
       return FN2_E_CUDA;
   }
-  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; }
+  for (int cls = P.ncls; cls < 4; ++cls) { P.a[cls] = P.a[0]; P.b[cls] = P.b[0]; P.bw[cls] = P.bw[0]; }
   static PerDeviceOnce once;
   const cudaError_t attr_err = per_device_once(once, [] {
     cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_x3_kernel<10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -708,15 +772,18 @@ int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float*
   P.nwork = 0;
   static PerDeviceOnce once_pair;
   const EnvSwitches& sw = env_switches();
-  if (P.TX == 1 && !sw.no_pair) {
-    // narrow images: persistent CTA pairs over the list of 4-row pair tiles
+  if (!sw.no_pair) {
+    // persistent CTA pairs over the list of pair tiles (4 a-rows x 32 columns)
     const cudaError_t pe = per_device_once(once_pair, [] {
-      cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_x3_pair_kernel<10>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)x3_pair_smem_bytes(MAX_KC));
+      cudaError_t e = cudaFuncSetAttribute(corr_tc_fwd_x3_pair_kernel<10, false>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)x3_pair_smem_bytes(MAX_KC));
+      if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(corr_tc_fwd_x3_pair_kernel<10, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)x3_pair_smem_bytes(MAX_KC));
       return e;
     });
     if (pe != cudaSuccess) { note_cuda_error(pe); (void)cudaGetLastError(); return FN2_E_CUDA; }
-    const long long nwork = (long long)g.N * P.ncls * P.TYP;
+    const long long nwork = (long long)g.N * P.ncls * P.TYP * P.TX;
     if (nwork > 0x3fffffffLL) return FN2_E_BAD_SHAPE;
     P.nwork = (int)nwork;
     const long long slots = std::max(1, device_sm_count() / 2);
@@ -733,7 +800,8 @@ int corr_tc_x3_forward(const CorrGeom& g, const float* a, const float* b, float*
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, corr_tc_fwd_x3_pair_kernel<10>, P);
+    const cudaError_t e = P.TX > 1 ? cudaLaunchKernelEx(&cfg, corr_tc_fwd_x3_pair_kernel<10, true>, P)
+                                   : cudaLaunchKernelEx(&cfg, corr_tc_fwd_x3_pair_kernel<10, false>, P);
     if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
     return after_launch();
   }
