@@ -15,8 +15,8 @@ python tools/time_ops.py 8 tf32x3 > gpurun_out/${T}_time_ops_x3_n8.jsonl 2>&1
 B="python bench.py --steps 2 --warmup 3 --no-extras --no-cpu-baseline --no-ref-gpu --no-e2e"
 $B > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -s 60 -c 60 --csv --log-file gpurun_out/${T}_launches.csv $B > gpurun_out/ncu_launches.log 2>&1
-bash tools/gpu_prof.sh x3_fwd corr_tc_fwd_x3 corr_fwd 32 tf32x3
-bash tools/gpu_prof.sh x3_bwd corr_tc_bwd corr_bwd 32 tf32x3
+bash tools/gpu_prof.sh x3_fwd corr_tc_fwd_x3_pair corr_fwd 32 tf32x3
+bash tools/gpu_prof.sh x3_bwd corr_tc_bwd_x3_pair corr_bwd 32 tf32x3
 bash tools/gpu_prof.sh corr_fwd corr_tc_fwd_pair corr_fwd 32 tf32
 bash tools/gpu_prof.sh corr_bwd corr_tc_bwd corr_bwd 32 tf32
 bash tools/gpu_prof.sh warp_fwd warp_tile_gather warp_fwd 32
