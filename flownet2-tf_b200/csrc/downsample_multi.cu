@@ -66,7 +66,6 @@ struct MsParams {
   int J[MS], L[MS];               // lanes per interval (a power of two <= 32), pixels per lane (a multiple of 4 / C)
   int tOff[MS + 1];               // first thread of scale s in a band CTA (multiples of 32)
   int pOff[MS], pTile;            // partial entries: offset of scale s inside a band's tile, entries per tile
-  int nw[MS], fOff[MS], fTile;    // warps of scale s in a band CTA; NaN-flag words: offset of scale s, words per tile
   int blkOff[MS + 1];             // combine kernel: first block of scale s within an image
   float hs[MS], ws[MS];
   float in_scale;                 // samples are multiplied by this on load (the loss's flow * 0.05), 1 = none
@@ -76,8 +75,6 @@ struct MsParams {
   float* dir[MS];                 // (pred - down) / epe per element (may be null)
   float* epe;                     // [ns] per-scale sum of end-point errors, divided by N (null without pred)
   size_t ctrlOff, partOff;        // byte offsets in the workspace: control block (ticket + block sums), partials
-  size_t partStride;              // floats between the four partial arrays (A values, B values, A NaN, B NaN)
-  size_t flagOff;                 // byte offset of the NaN flags: one word per (band, scale, output row, warp)
 };
 
 // Shared-memory layout of the band kernel (bytes); used by the host for the launch size.
@@ -169,10 +166,7 @@ __device__ __forceinline__ void add_entry(float (&acc)[NV], const float* e) {
 
 // ------------------------------------------------------------------------------------------------- band walk
 // CT channels; PXV = 4 / CT pixels per 16-byte vector; a thread owns at most NVEC vectors (P pixels) of every row.
-// Partials of (band, scale, output row, interval dx) live in four arrays of CT floats per entry: A values, B values, A NaN
-// weights, B NaN weights.  The NaN arrays are only written (and read by the combine kernel) when the storing warp has
-// met a NaN in the band; a flag word per (band, scale, output row, warp) says so -- NaN-free input moves 16 bytes per
-// entry instead of 32 and the combine reads a quarter of what packed entries cost.
+// Partial entry of (band, scale, output row, interval dx): [A values x CT, A NaN weights x CT, B values, B NaN weights].
 template <int CT, bool SCALED>
 __global__ void __launch_bounds__(1024, 1) ms_band_kernel(MsParams p, const float* __restrict__ in,
                                                           float* __restrict__ ws) {
@@ -268,10 +262,7 @@ __global__ void __launch_bounds__(1024, 1) ms_band_kernel(MsParams p, const floa
 
   const float scale = p.in_scale;
   float* part = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + p.partOff) +
-                (((size_t)n * p.nbands + band) * p.pTile + p.pOff[s]) * CT;
-  int* flags = reinterpret_cast<int*>(reinterpret_cast<char*>(ws) + p.flagOff) +
-               ((size_t)n * p.nbands + band) * p.fTile + p.fOff[s];
-  const int wis = local >> 5;                                 // this warp's index inside its scale
+                (((size_t)n * p.nbands + band) * p.pTile + p.pOff[s]) * NE;
   const int d_first = rowD[s * RB];
   const float4* vbase = reinterpret_cast<const float4*>(bandbuf) + vec0;
   const int rowv = rowf / 4;                                  // 16-byte vectors per row
@@ -313,8 +304,7 @@ __global__ void __launch_bounds__(1024, 1) ms_band_kernel(MsParams p, const floa
     float v[NE];
 #pragma unroll
     for (int c = 0; c < CT; ++c) { v[c] = accA[k][c]; v[CT + c] = 0.f; v[2 * CT + c] = accB[k][c]; v[3 * CT + c] = 0.f; }
-    const bool anym = __any_sync(FULL, marked != 0);
-    if (anym) {                                               // rare: rebuild the NaN weights from the marked rows
+    if (__any_sync(FULL, marked != 0)) {                      // rare: rebuild the NaN weights from the marked rows
       for (int i = 0; i < nrows; ++i) {
         if (!((marked >> i) & 1u)) continue;
         const int d = rowD[s * RB + i];
@@ -329,35 +319,13 @@ __global__ void __launch_bounds__(1024, 1) ms_band_kernel(MsParams p, const floa
     }
     for (int off = J >> 1; off >= 1; off >>= 1) {             // the J lanes of an interval, a fixed tree
 #pragma unroll
-      for (int c = 0; c < CT; ++c) {
-        v[c] += __shfl_xor_sync(FULL, v[c], off);
-        v[2 * CT + c] += __shfl_xor_sync(FULL, v[2 * CT + c], off);
-      }
-      if (anym) {
-#pragma unroll
-        for (int c = 0; c < CT; ++c) {
-          v[CT + c] += __shfl_xor_sync(FULL, v[CT + c], off);
-          v[3 * CT + c] += __shfl_xor_sync(FULL, v[3 * CT + c], off);
-        }
-      }
+      for (int e = 0; e < NE; ++e) v[e] += __shfl_xor_sync(FULL, v[e], off);
     }
-    const int slot = dy - d_first;
     if (active && j == 0) {
-      float* e = part + ((size_t)slot * oW + dx) * CT;
-      if constexpr (CT == 2) {
-        *reinterpret_cast<float2*>(e) = make_float2(v[0], v[1]);
-        *reinterpret_cast<float2*>(e + p.partStride) = make_float2(v[4], v[5]);
-        if (anym) {
-          *reinterpret_cast<float2*>(e + 2 * p.partStride) = make_float2(v[2], v[3]);
-          *reinterpret_cast<float2*>(e + 3 * p.partStride) = make_float2(v[6], v[7]);
-        }
-      } else {
-        e[0] = v[0];
-        e[p.partStride] = v[2];
-        if (anym) { e[2 * p.partStride] = v[1]; e[3 * p.partStride] = v[3]; }
-      }
+      float* e = part + ((size_t)(dy - d_first) * oW + dx) * NE;
+      *reinterpret_cast<float4*>(e) = make_float4(v[0], v[1], v[2], v[3]);
+      if constexpr (NE == 8) *reinterpret_cast<float4*>(e + 4) = make_float4(v[4], v[5], v[6], v[7]);
     }
-    if (lane == 0 && wis < p.nw[s]) flags[slot * p.nw[s] + wis] = anym ? 1 : 0;
   };
 
   // ---- walk the rows ----
@@ -433,31 +401,13 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
     float acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;
-    const float* base = parts + ((size_t)n * p.nbands * p.pTile + p.pOff[s] + dx) * CT;
-    const size_t bstride = (size_t)p.pTile * CT;
-    const int* fl = reinterpret_cast<const int*>(reinterpret_cast<const char*>(ws) + p.flagOff) +
-                    (size_t)n * p.nbands * p.fTile + p.fOff[s];
-    const int nws = p.nw[s];
-    const int wA = (dx * p.J[s]) >> 5, wB = dx > 0 ? ((dx - 1) * p.J[s]) >> 5 : 0;   // the warps that stored them
-    auto add = [&](float* dst, const float* src) {
-      if constexpr (CT == 2) {
-        const float2 t = *reinterpret_cast<const float2*>(src);
-        dst[0] += t.x; dst[1] += t.y;
-      } else {
-        dst[0] += *src;
-      }
-    };
+    const float* base = parts + ((size_t)n * p.nbands * p.pTile + p.pOff[s] + dx) * (2 * NV);
+    const size_t bstride = (size_t)p.pTile * (2 * NV);
 #pragma unroll 4
     for (int b = br.x; b <= br.y; ++b) {                     // the bands that feed this row, in band order
-      const int slot = dy - dfirst[b];
-      const float* e = base + b * bstride + (size_t)slot * oW * CT;
-      const int* f = fl + (size_t)b * p.fTile + slot * nws;
-      add(acc, e);                                           // A part of this column's own interval
-      if (f[wA]) add(acc + CT, e + 2 * p.partStride);
-      if (dx > 0) {                                          // B part of the interval to its left
-        add(acc, e - CT + p.partStride);
-        if (f[wB]) add(acc + CT, e - CT + 3 * p.partStride);
-      }
+      const float* e = base + b * bstride + (size_t)(dy - dfirst[b]) * oW * (2 * NV);
+      add_entry<NV>(acc, e);                                 // A part of this column's own interval
+      if (dx > 0) add_entry<NV>(acc, e - NV);                // B part of the interval to its left
     }
     const float tot = __ldg(ws + p.t.totY[s] + dy) * __ldg(ws + p.t.totX[s] + dx);
     const size_t o = (((size_t)n * oH + dy) * oW + dx) * CT;
@@ -527,7 +477,7 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   p.N = N; p.iH = iH; p.iW = iW; p.ns = ns;
   p.nbands = (iH + RB - 1) / RB;
   if (p.nbands > MAXBANDS) return false;
-  int words = 0, pt = 0, blk = 0, thr = 0, ft = 0;
+  int words = 0, pt = 0, blk = 0, thr = 0;
   auto take = [&](int n) { const int at = words; words += (n + 3) / 4 * 4; return at; };   // 16-byte aligned tables
   for (int s = 0; s < ns; ++s) {
     const int oH = out_hw[2 * s], oW = out_hw[2 * s + 1];
@@ -551,9 +501,6 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
     thr += (oW * J + 31) / 32 * 32;
     p.pOff[s] = pt;
     pt += p.maxRows[s] * oW;
-    p.nw[s] = (oW * J + 31) / 32;
-    p.fOff[s] = ft;
-    ft += p.maxRows[s] * p.nw[s];
     p.blkOff[s] = blk;
     blk += (oH * oW + CB - 1) / CB;
   }
@@ -561,11 +508,9 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   p.nthr = thr;
   for (int s = ns; s < MS; ++s) {   // unused scales
     p.oH[s] = p.oW[s] = 2; p.J[s] = 1; p.L[s] = px; p.maxRows[s] = 0; p.pOff[s] = pt; p.hs[s] = p.ws[s] = 2.f;
-    p.nw[s] = 0; p.fOff[s] = ft;
   }
   for (int s = ns; s <= MS; ++s) { p.blkOff[s] = blk; p.tOff[s] = thr; }
   p.pTile = pt;
-  p.fTile = ft;
   // table area
   for (int s = 0; s < ns; ++s) { p.t.rowW[s] = take(2 * iH); p.t.rowD[s] = take(iH); }
   for (int s = 0; s < ns; ++s) p.t.colW[s] = take(2 * iW);
@@ -580,9 +525,7 @@ bool ms_plan(MsParams* pp, const int* out_hw, int ns, int N, int iH, int iW, int
   if (nblocks > 0x7fffffffLL) return false;
   p.ctrlOff = align_up((size_t)words * 4, 256);
   p.partOff = align_up(p.ctrlOff + 16 + (size_t)nblocks * 4, 256);
-  p.partStride = (size_t)N * p.nbands * p.pTile * C;
-  p.flagOff = align_up(p.partOff + 4 * p.partStride * sizeof(float), 256);
-  *ws_bytes = p.flagOff + (size_t)N * p.nbands * p.fTile * sizeof(int);
+  *ws_bytes = p.partOff + (size_t)N * p.nbands * p.pTile * (4 * C) * sizeof(float);
   *band_smem = band_smem_layout(iW * C).total;
   return *band_smem <= 100 * 1024;                 // the whole band stays resident (two CTAs per SM at least)
 }
