@@ -271,3 +271,39 @@ def test_first_cuda_action_of_a_fresh_thread_is_one_of_our_launches():
     wga, wgb = o.c_correlation_grad(go.cpu().numpy(), a.numpy(), b.numpy(), 1, 20, 1, 2, 20, f64=True)
     assert_close(res["grads"][0].cpu().numpy(), wga)
     assert_close(res["grads"][1].cpu().numpy(), wgb)
+
+
+def test_more_than_2_to_the_31_elements():
+    """Maximum sizes: a cost volume of 1600 x 48 x 64 x 441 = 2.17e9 elements (8.7 GB) -- every index past 2^31 must
+    be formed in 64 bits.  Images are independent, so a batch made of four distinct pairs repeated 400 times must
+    reproduce the four-pair result bit for bit, in the forward and in both gradients, at the start, around the 2^31st
+    element (image 1585) and at the end."""
+    if torch.cuda.get_device_properties(0).total_memory < 80e9:
+        pytest.skip("needs ~45 GB of device memory")
+    reps, base_n = 400, 4
+    a4, b4 = corr_inputs(base_n, 48, 64, 256)
+    g4 = grad_like((base_n, 48, 64, 441))
+    a4, b4, g4 = a4.cuda(), b4.cuda(), g4.cuda()
+    out4 = fn2.correlation(a4, b4, 1, 20, 1, 2, 20)
+    ga4, gb4 = fn2.correlation_grad(g4, a4, b4, 1, 20, 1, 2, 20)
+    a, b = a4.repeat(reps, 1, 1, 1), b4.repeat(reps, 1, 1, 1)
+    out = fn2.correlation(a, b, 1, 20, 1, 2, 20)
+    assert out.numel() > 2 ** 31
+    picks = [0, 1, 2, 3, 1584, 1585, 1586, 1587, 1596, 1597, 1598, 1599]
+    for n in picks:
+        assert torch.equal(out[n], out4[n % base_n]), n
+    g = g4.repeat(reps, 1, 1, 1)
+    del out
+    ga, gb = fn2.correlation_grad(g, a, b, 1, 20, 1, 2, 20)
+    for n in picks:
+        assert torch.equal(ga[n], ga4[n % base_n]) and torch.equal(gb[n], gb4[n % base_n]), n
+    del a, b, g, ga, gb
+    # flow_warp: 3700 images of 384 x 512 x 3 = 2.18e9 elements
+    img2, flo2 = torch.rand(2, 384, 512, 3, device="cuda"), torch.randn(2, 384, 512, 2, device="cuda") * 8
+    w2 = fn2.flow_warp(img2, flo2)
+    n_img = 3700
+    w = fn2.flow_warp(img2.repeat(n_img // 2, 1, 1, 1), flo2.repeat(n_img // 2, 1, 1, 1))
+    assert w.numel() > 2 ** 31
+    for n in (0, 1, 3640, 3641, 3642, 3698, 3699):
+        assert torch.equal(w[n], w2[n % 2]), n
+    torch.cuda.empty_cache()
