@@ -20,11 +20,21 @@ events), so the host never blocks and the whole step can be captured in a CUDA g
 path at all (``src/net.py`` builds one graph on one device); this is the B200-side extension BASELINE.json's
 north_star asks for.  ``correlation_strips`` is a ``torch.autograd.Function``: differentiable end to end.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
 from . import _lib
 from .correlation import _check_pair, _prec, _workspace, output_shape
+
+
+#: Strips shorter than this run the exchange first and ONE kernel over the whole strip instead of overlapping the
+#: exchange with the interior rows (three kernels per pass).  Overlap only pays when the interior is a launch of its
+#: own worth: at the 4K conv3 shape (strips of 136 / 68 / 34 rows) the split costs more than the 0.05 - 0.14 ms exchange
+#: it hides: 4 strips of 68 rows 0.61 ms plain against 0.67 overlapped (split-tf32), 2 strips of 136 rows 0.88 against 0.87
+#: (bench.py --config strips4k; DESIGN.md section 6).
+OVERLAP_MIN_ROWS = int(os.environ.get("FN2_STRIPS_OVERLAP_MIN_ROWS", "100"))
 
 
 def halo_rows(max_displacement, stride_2):
@@ -191,7 +201,8 @@ class _CorrelationStrips(torch.autograd.Function):
         # rows [i0, i1) need no halo: computed while the exchange is in flight
         i0, i1 = (h if top else 0), (H - h if bottom else H)
         # (needs 2h own rows for a boundary band, and row slices that stay 16-byte aligned)
-        overlap = bool(direct and reqs and H >= 2 * h and i1 - i0 >= 2 * s2 and (W * C) % 4 == 0)
+        overlap = bool(direct and reqs and H >= 2 * h and i1 - i0 >= 2 * s2 and (W * C) % 4 == 0
+                       and H >= OVERLAP_MIN_ROWS)
         if overlap:
             fwd(_rows(a, i0, i1), _rows(own, i0 - (h if top else 0), i1 + (h if bottom else 0)), k, md, s1, s2, pad,
                 h if top else 0, h if bottom else 0, precision, out=_rows(out, i0, i1))

@@ -29,11 +29,12 @@ def _bounds(H, world):
     return edges
 
 
-def _worker(rank, world, port, H, W, C, outdir):
+def _worker(rank, world, port, H, W, C, outdir, overlap):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         import flownet2_tf_b200.strips as strips
+        strips.OVERLAP_MIN_ROWS = 0 if overlap else 10 ** 9    # force either schedule, whatever the strip height
         a, b = corr_inputs(1, H, W, C)
         e = _bounds(H, world)
         a_s = a[:, e[rank]:e[rank + 1]].clone().requires_grad_()
@@ -47,13 +48,15 @@ def _worker(rank, world, port, H, W, C, outdir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,H", [(2, 44), (3, 66), (2, 41),      # strips shorter than 2 halos: exchange, then one call
-                                     (2, 100), (3, 150)])             # interior rows computed under the exchange
-def test_strips_reproduce_whole_image_op(tmp_path, world, H):
+@pytest.mark.parametrize("world,H,overlap", [
+    (2, 44, True), (3, 66, True), (2, 41, True),      # strips shorter than 2 halos: exchange, then one call, always
+    (2, 100, True), (3, 150, True),                   # interior rows computed under the exchange
+    (2, 100, False)])                                 # the same strips, exchange first and one call
+def test_strips_reproduce_whole_image_op(tmp_path, world, H, overlap):
     from oracle import oracle as o
     W, C = 10, 4
     port = _free_port()
-    mp.spawn(_worker, args=(world, port, H, W, C, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, port, H, W, C, str(tmp_path), overlap), nprocs=world, join=True)
     a, b = corr_inputs(1, H, W, C)
     g = grad_like((1, H, W, 441))
     want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
