@@ -28,11 +28,16 @@ using namespace tc;
 
 template <int C>
 struct Win {
-  // margins sized so the window fits ~110 KB (two CTAs per SM): C <= 3 -> 77 x 120 pixels, C == 4 -> 65 x 104
-  static constexpr int MY = (C <= 3) ? 22 : 16;
-  static constexpr int MX = (C <= 3) ? 24 : 16;
+  // C <= 3: margins 12 x 12 -> 57 x 96 pixels = 66 KB (three CTAs per SM); C == 4: 16 x 16 -> 65 x 104 pixels
+#ifndef FN2_WIN_MY   // developer A/B of the gather window (variant builds, tools/gpu_ab.sh)
+#define FN2_WIN_MY 12   // measured (tools/time_warp.py, N=32; forward / backward ms): margins 22x24 0.0589 / 0.218 on
+#define FN2_WIN_MX 12   // N(0, 8 px) flows and 0.0675 / 0.209 on the reference's sample flow; 16x16 0.0576 / 0.208 and
+#define FN2_WIN_COLS 96 // 0.0654 / 0.201; 12x12 0.0583 / 0.2105 and 0.0607 / 0.195; 8x8 0.0613 / 0.216 and 0.0628 / 0.194
+#endif
+  static constexpr int MY = (C <= 3) ? FN2_WIN_MY : 16;
+  static constexpr int MX = (C <= 3) ? FN2_WIN_MX : 16;
   static constexpr int ROWS = TH + 2 * MY + 1;
-  static constexpr int COLS = (C <= 3) ? 120 : 104;                  // >= TW + 2*MX + 1
+  static constexpr int COLS = (C <= 3) ? FN2_WIN_COLS : 104;                  // >= TW + 2*MX + 1
   static constexpr int NB = (COLS * C + 255) / 256;                  // TMA boxes (inner box dimension <= 256 elements)
   static constexpr int PXB = COLS / NB;                              // pixels per box
   static constexpr int BW = PXB * C;                                 // floats per box row
