@@ -26,6 +26,10 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = epilogue (one
 // per TMEM lane quadrant), warps 6-9 = converters.
+//
+// What ships by default is the CTA-PAIR version further down (corr_tc_fwd_x3_pair_kernel: cta_group::2, M256 N256,
+// persistent, narrow and wide images; 0.210 ms at N = 32 against 0.343 for the single-CTA kernel described above, which
+// stays as the FN2_NO_PAIR developer fallback and as the plain statement of the scheme).
 #include <algorithm>
 #include "fn2_tc.cuh"
 
