@@ -603,4 +603,60 @@ int multiscale_forward(const float* in, float in_scale, float* const* outs, cons
   return FN2_OK;
 }
 
+// ------------------------------------------------------------------------------------------- built-in scratch
+// fn2_downsample_multi_forward_noalloc (fn2ops.h): the same three kernels, for callers that cannot hand over a
+// workspace because they have no way of getting device memory (a ctypes stub inside a TensorFlow process, whose
+// allocator has taken the GPU's memory for itself and is not reachable from Python; any plug-in host that passes inputs
+// and outputs only).  The scratch then lives in the library image: every GPU that loads libfn2ops.so carries these
+// bytes until the process exits, whether the entry point is used or not.
+//
+// g_ms_builtin_scratch is a DEVICE array.  Kernels of this file could name it directly; host code cannot: on the host
+// the identifier is only a handle for the runtime's symbol calls, and handing it to a kernel as if it were a pointer
+// would make the kernel fault (or scribble over host memory where the GPU can reach it).  The address that kernels can
+// use comes from cudaGetSymbolAddress, differs from device to device, and is looked up once per device ordinal by
+// whichever call gets there first, with that device current.
+namespace {
+
+constexpr size_t MS_BUILTIN_BYTES = FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES;
+static __device__ __align__(256) unsigned char g_ms_builtin_scratch[MS_BUILTIN_BYTES];
+
+std::atomic<void*> g_ms_builtin_ptr[FN2_MAX_DEVICES];   // device address of the array, per device ordinal (null = not asked yet)
+
+int ms_builtin_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { note_cuda_error(e); (void)cudaGetLastError(); return FN2_E_CUDA; }
+  const bool tracked = dev >= 0 && dev < FN2_MAX_DEVICES;
+  void* ptr = tracked ? g_ms_builtin_ptr[dev].load(std::memory_order_acquire) : nullptr;
+  if (!ptr) {
+    // not an allocation: the array is part of the module; this asks where the module put it on the current device.
+    // Two threads racing here get the same answer.
+    e = cudaGetSymbolAddress(&ptr, g_ms_builtin_scratch);
+    if (e != cudaSuccess || !ptr) {
+      note_cuda_error(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+      (void)cudaGetLastError();
+      return FN2_E_CUDA;
+    }
+    if (tracked) g_ms_builtin_ptr[dev].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return FN2_OK;
+}
+
+}  // namespace
+
+// The array keeps the previous call's tables, partial sums and block sums.  Nothing of that is read before this call
+// has rewritten it: ms_tables_kernel rebuilds every table entry and zeroes the combine ticket (the one word that must
+// start at zero) as its first act, in stream order ahead of the band and combine kernels; the band kernel writes
+// every partial the combine kernel reads.  That holds only while calls do not overlap on the GPU (see fn2ops.h).
+int multiscale_forward_noalloc(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
+                               int iW, int C, cudaStream_t st) {
+  if (multiscale_workspace_bytes(out_hw, num_scales, N, iH, iW, C) > MS_BUILTIN_BYTES) return FN2_E_BUILTIN_SCRATCH;
+  void* ws = nullptr;
+  const int rc = ms_builtin_scratch(&ws);
+  if (rc != FN2_OK) return rc;
+  return multiscale_forward(in, 1.0f, outs, nullptr, nullptr, nullptr, out_hw, num_scales, N, iH, iW, C, ws,
+                            MS_BUILTIN_BYTES, st);
+}
+
 }  // namespace fn2

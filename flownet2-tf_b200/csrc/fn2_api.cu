@@ -117,6 +117,10 @@ const char* fn2_error_string(int status) {
     case FN2_E_UNSUPPORTED_GEOMETRY:
       return "unsupported geometry (row halos need kernel_size 1, stride_1 1, pad == max_displacement and "
              "halo_top % stride_2 == 0; the fused loss needs C <= 2, in_w * C % 4 == 0 and reductions by >= 1.5)";
+    case FN2_E_BUILTIN_SCRATCH:
+      return "these shapes need more scratch than the 16 MiB array built into the library "
+             "(fn2_downsample_multi_workspace_bytes > FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES): use a smaller batch, "
+             "or fn2_downsample_multi_forward with a caller-provided workspace";
     default: return "unknown fn2 status";
   }
 }
@@ -322,6 +326,18 @@ int fn2_downsample_multi_forward(const float* in, float* const* outs, const int*
   if (ws_bytes && (!ws || !aligned16(ws))) return FN2_E_BAD_POINTER;
   return multiscale_forward(in, 1.0f, outs, nullptr, nullptr, nullptr, out_hw, num_scales, N, iH, iW, C, ws, ws_bytes,
                             static_cast<cudaStream_t>(stream));
+}
+
+// No workspace argument and no allocation: the scratch is the library's own device array (downsample_multi.cu), for
+// callers that have no device memory to give.  The first call on a device also finds out where that array lives there.
+int fn2_downsample_multi_forward_noalloc(const float* in, float* const* outs, const int* out_hw, int num_scales, int N,
+                                         int iH, int iW, int C, void* stream) {
+  const int rc = check_scales(out_hw, num_scales, N, iH, iW, C);
+  if (rc != FN2_OK) return rc;
+  if (!in || !outs || !aligned16(in)) return FN2_E_BAD_POINTER;
+  for (int s = 0; s < num_scales; ++s)
+    if (!outs[s] || !aligned16(outs[s])) return FN2_E_BAD_POINTER;
+  return multiscale_forward_noalloc(in, outs, out_hw, num_scales, N, iH, iW, C, static_cast<cudaStream_t>(stream));
 }
 
 int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float* const* preds, const int* out_hw,

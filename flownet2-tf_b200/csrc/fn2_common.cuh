@@ -106,6 +106,9 @@ size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int 
 int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
                        float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
                        int C, void* ws, size_t ws_bytes, cudaStream_t st);
+// the plain multi-scale downsample with its scratch in the library's own device array (no workspace argument)
+int multiscale_forward_noalloc(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
+                               int iW, int C, cudaStream_t st);
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 // floor / ceil division for possibly negative numerators (b > 0)

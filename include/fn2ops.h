@@ -12,6 +12,7 @@
  *     pointer after returning, and fully defines every output element (no pre-zeroing needed).
  *   - Every call only enqueues work on `stream` (a cudaStream_t passed as void*; NULL = legacy default
  *     stream) and returns without synchronising; calls are re-entrant and CUDA-graph capturable.
+ *     (fn2_downsample_multi_forward_noalloc keeps its scratch inside the library and states its own rules.)
  *   - Return value: FN2_OK (0) or a negative fn2_status.  Nothing throws, prints or exits.
  *   - Element counts above 2^31 are supported (64-bit indexing); each single dimension must fit in int.
  */
@@ -46,9 +47,11 @@ typedef enum fn2_status {
                                   (downsample_kernel_gpu.cu.cc:40-41,92-93); rejected instead           */
   FN2_E_CUDA = -10,            /* a CUDA runtime/driver call failed; see fn2_last_cuda_error()          */
   FN2_E_NO_DEVICE = -11,       /* no sm_100 device is current                                           */
-  FN2_E_UNSUPPORTED_GEOMETRY = -12 /* *_halo entry points: need kernel_size 1, stride_1 1, pad == max_displacement,
+  FN2_E_UNSUPPORTED_GEOMETRY = -12,/* *_halo entry points: need kernel_size 1, stride_1 1, pad == max_displacement,
                                   halo_top a multiple of stride_2; fn2_multiscale_epe_forward: shapes the
                                   fused multi-scale kernels do not take                                 */
+  FN2_E_BUILTIN_SCRATCH = -13  /* fn2_downsample_multi_forward_noalloc: the shapes need more scratch than the
+                                  library's built-in array holds (FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES)  */
 } fn2_status;
 
 /* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode.
@@ -200,6 +203,34 @@ FN2_API int fn2_downsample_multi_forward(const float* input, float* const* outpu
 /* Scratch bytes of the two multi-scale entry points (tables that depend on the shapes only, and the per-tile partial
  * sums of the band pass).  0 when every scale goes through the single-scale kernels (C > 2, upsampling, odd widths). */
 FN2_API size_t fn2_downsample_multi_workspace_bytes(const int* out_hw, int num_scales, int N, int in_h, int in_w, int C);
+
+/* fn2_downsample_multi_forward for callers that have no device buffer to hand over as `workspace`.  It has no
+ * counterpart in the reference (whose five downsample() calls need no scratch at all); it exists for the binding
+ * INTEGRATION.md section 1 describes.  A ctypes stub living inside a TensorFlow process sees only the tensors the
+ * graph gives it: TensorFlow's allocator has already reserved (by default nearly all of) the GPU's memory for itself,
+ * so a cudaMalloc from the stub fails or eats into what is left for the driver, and allocate_temp is out of reach from
+ * Python.  The same holds for any host that gives a plug-in its inputs and outputs and nothing else.  Such callers
+ * cannot use fn2_downsample_multi_forward, which asks them for fn2_downsample_multi_workspace_bytes() of scratch.
+ *
+ * This variant takes the same inputs and outputs and runs the same kernels, with the scratch (weight tables, per-band
+ * partial sums, a small control block) placed in an array that is part of the library image itself:
+ * FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES of device memory on every GPU that loads libfn2ops.so, held until the
+ * process exits.  It calls no cudaMalloc / cudaFree and nothing that allocates on its behalf.
+ *
+ *   - Limit: calls whose fn2_downsample_multi_workspace_bytes() exceeds the array are refused with
+ *     FN2_E_BUILTIN_SCRATCH before anything is enqueued (16 MiB covers the loss sizes of flownet_c.py:135-160 on
+ *     384 x 512 x 2 flows up to a batch of 18; shapes that go through the single-scale kernels need no scratch
+ *     and always fit).
+ *   - First call on each device: the library looks up where the array lives on the CURRENT device (a driver query that
+ *     may also load the kernels' module) and remembers it per device ordinal.  Make that first call during set-up, on
+ *     the device that will be used, before any stream capture is begun.
+ *   - One array per device, shared by every call: two calls that can overlap on the GPU (different streams, or different
+ *     host threads on different streams) race on it and corrupt each other's results.  Issue them on one stream, or
+ *     order them with events.  Calls on one stream need nothing: the array keeps whatever the previous call left, and
+ *     every call rewrites the tables and partial sums it reads and resets its control word, in stream order. */
+#define FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES (16u * 1024u * 1024u)
+FN2_API int fn2_downsample_multi_forward_noalloc(const float* input, float* const* outputs, const int* out_hw,
+                                         int num_scales, int N, int in_h, int in_w, int C, void* stream);
 
 /* The data term of the multi-scale training loss in the same pass (second half).  Replaces,
  * for every scale s, the graph nodes of flownet_c.py:127-160 + utils.py:209-224:
