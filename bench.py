@@ -287,7 +287,9 @@ def load_peaks():
 def strips_bench(torch, dist, fn2, dev, rank, world, precision, steps, warm, hbm_peak):
     """BASELINE config 5: ONE 4K pair's conv3 correlation [1,272,480,256], forward + backward, cut into `world` row
     strips (strong scaling); the halo rows of input_b and the mirror halo of backprops_b travel by NCCL send/recv inside
-    the timed region, overlapped with the interior rows (flownet2_tf_b200.strips)."""
+    the timed region.  Strips of >= 100 rows (2 GPUs: 136) overlap the exchange with their interior rows; the 68- and
+    34-row strips of 4 and 8 GPUs exchange first and run one kernel per pass (flownet2_tf_b200.strips.overlap_used; the
+    line says which under collective.overlap)."""
     from flownet2_tf_b200 import strips
     if H4K % world != 0 or (H4K // world) % 2 != 0 or H4K // world < 20:
         return {"unavailable": "272 rows do not split into %d even strips of >= 20 rows" % world}
@@ -396,7 +398,10 @@ def strips_bench(torch, dist, fn2, dev, rank, world, precision, steps, warm, hbm
             "what": "ncclSend/ncclRecv (torch.distributed batch_isend_irecv), 20 rows of input_b per direction per "
                     "boundary in forward, 20 rows of backprops_b partial sums in backward",
             "bytes_per_direction_per_boundary": 20 * W4K * CC * 4, "comm_nranks": world,
-            "exchange_alone_ms": round(comm_ms, 4), "overlapped_with": "interior rows of the strip"},
+            "exchange_alone_ms": round(comm_ms, 4),
+            "overlap": bool(strips.overlap_used(1, rows, W4K, CC, 20, 2, rank, world)),
+            "overlap_note": "true: the exchange runs under the strip's interior rows; false: exchange first, then "
+                            "one kernel over the strip (strips under %d rows)" % strips.OVERLAP_MIN_ROWS},
         "launch": "one CUDA graph per step (kernels + NCCL send/recv captured)" if graph_ms is not None
                   else "eager autograd calls (correlation_strips forward + backward)",
         "ms_per_step_eager": round(eager_ms, 4), "graph_note": graph_note,

@@ -6,12 +6,16 @@ The image height is cut into ``world`` horizontal strips, one per rank (rank 0 =
 
   forward : every rank sends its top ``h`` rows of ``b`` to the rank above and its bottom ``h`` rows to the rank
             below (``torch.distributed`` P2P: NCCL send/recv over NVLink on GPUs, gloo in the CPU tests); the halos
-            land directly in a tall copy of ``b`` (no concatenation).  WHILE the exchange is in flight the rows that
-            need no halo -- all but the first and last ``h`` of the strip -- are computed; the two boundary bands
-            follow once the halos have arrived (``fn2_correlation_forward_halo`` on row slices).  The image border
-            uses no halo: rows beyond the tall ``b`` are the op's zero padding.
-  backward: ``backprops_a`` needs the same halo of ``b`` (kept from the forward).  The boundary bands are computed
-            FIRST: their ``backprops_b`` covers the neighbours' halo rows, partial sums the owners must add, so the
+            land directly in a tall copy of ``b`` (no concatenation).  For strips of at least ``OVERLAP_MIN_ROWS``
+            (100) rows and a batch of one, the rows that need no halo -- all but the first and last ``h`` of the
+            strip -- are computed WHILE the exchange is in flight and the two boundary bands follow once the halos
+            have arrived (``fn2_correlation_forward_halo`` on row slices).  Shorter strips (the 68- and 34-row strips
+            of a 4K pair on 4 and 8 GPUs) wait for the exchange and run ONE kernel over the whole strip, which
+            measured faster there; batches above one do the same and also stage the halos through contiguous
+            buffers.  ``overlap_used`` tells which schedule a shape gets.  The image border uses no halo: rows
+            beyond the tall ``b`` are the op's zero padding.
+  backward: ``backprops_a`` needs the same halo of ``b`` (kept from the forward).  With the overlapped schedule the
+            boundary bands are computed FIRST: their ``backprops_b`` covers the neighbours' halo rows, partial sums the owners must add, so the
             mirror exchange starts as soon as the bands are done and the interior rows are computed under it
             (2 x 9.83 MB per boundary at 4K instead of shipping 441-channel gradient halos).
 
@@ -35,6 +39,22 @@ from .correlation import _check_pair, _prec, _workspace, output_shape
 #: it hides: 4 strips of 68 rows 0.61 ms plain against 0.67 overlapped (split-tf32), 2 strips of 136 rows 0.88 against 0.87
 #: (bench.py --config strips4k).
 OVERLAP_MIN_ROWS = int(os.environ.get("FN2_STRIPS_OVERLAP_MIN_ROWS", "100"))
+
+
+def _overlap_decision(N, H, W, C, h, s2, top, bottom):
+    """True when a strip of this shape overlaps the exchange with its interior rows: a batch of one (row slices stay
+    contiguous), 2h own rows for a boundary band, an interior worth a launch, row slices that stay 16-byte aligned, and
+    at least OVERLAP_MIN_ROWS rows (shorter strips measured faster with one kernel after the exchange)."""
+    i0, i1 = (h if top else 0), (H - h if bottom else H)
+    return bool(N == 1 and (top or bottom) and H >= 2 * h and i1 - i0 >= 2 * s2 and (W * C) % 4 == 0
+                and H >= OVERLAP_MIN_ROWS)
+
+
+def overlap_used(N, H, W, C, max_displacement, stride_2, rank, world):
+    """Whether ``correlation_strips`` overlaps the halo exchange with the interior rows for a [N,H,W,C] strip held by
+    ``rank`` of ``world`` (False: exchange first, then one kernel over the whole strip).  bench.py reports it."""
+    h = halo_rows(max_displacement, stride_2)
+    return _overlap_decision(N, H, W, C, h, stride_2, h if rank > 0 else 0, h if rank < world - 1 else 0)
 
 
 def halo_rows(max_displacement, stride_2):
@@ -200,9 +220,7 @@ class _CorrelationStrips(torch.autograd.Function):
         out = torch.empty((N, oh, ow, oc), dtype=a.dtype, device=a.device)
         # rows [i0, i1) need no halo: computed while the exchange is in flight
         i0, i1 = (h if top else 0), (H - h if bottom else H)
-        # (needs 2h own rows for a boundary band, and row slices that stay 16-byte aligned)
-        overlap = bool(direct and reqs and H >= 2 * h and i1 - i0 >= 2 * s2 and (W * C) % 4 == 0
-                       and H >= OVERLAP_MIN_ROWS)
+        overlap = bool(reqs) and _overlap_decision(N, H, W, C, h, s2, top, bottom)
         if overlap:
             fwd(_rows(a, i0, i1), _rows(own, i0 - (h if top else 0), i1 + (h if bottom else 0)), k, md, s1, s2, pad,
                 h if top else 0, h if bottom else 0, precision, out=_rows(out, i0, i1))
