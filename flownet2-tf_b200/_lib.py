@@ -14,6 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FN2_OPS_LIBRARY") or os.path.join(_HERE, "libfn2ops.so")
 CSRC_DIR = os.path.join(_HERE, "csrc")
 
+ABI_VERSION = 2   # FN2_ABI_VERSION of include/fn2ops.h this table was written against
+
 PRECISIONS = {"fp32": 0, "tf32": 1, "tf32x3": 3}
 
 _lock = threading.Lock()
@@ -48,6 +50,7 @@ _SIGNATURES = {
     "fn2_downsample_multi_forward_noalloc": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)]
                                              + [c_int] * 5 + [c_void_p]),
     "fn2_downsample_multi_workspace_bytes": (c_size_t, [ctypes.POINTER(c_int)] + [c_int] * 5),
+    "fn2_multiscale_epe_supported": (c_int, [ctypes.POINTER(c_int)] + [c_int] * 5),
     "fn2_multiscale_epe_forward": (c_int, [c_void_p, ctypes.c_float, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)]
                                    + [c_int] * 5 + [ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p), c_void_p,
                                                     c_void_p, c_size_t, c_void_p]),
@@ -82,8 +85,9 @@ def lib():
             for name, (restype, argtypes) in _SIGNATURES.items():
                 fn = getattr(handle, name)
                 fn.restype, fn.argtypes = restype, argtypes
-            if handle.fn2_abi_version() != 1:
-                raise RuntimeError("libfn2ops.so ABI version mismatch")
+            if handle.fn2_abi_version() != ABI_VERSION:
+                raise RuntimeError("libfn2ops.so has ABI version %d, this binding was written for %d: rebuild it "
+                                   "(make -C %s)" % (handle.fn2_abi_version(), ABI_VERSION, CSRC_DIR))
             _lib = handle
     return _lib
 

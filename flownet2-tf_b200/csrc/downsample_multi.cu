@@ -569,6 +569,17 @@ size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int 
   return best;
 }
 
+// Whether EVERY group of (up to five) scales takes the fused kernels: what fn2_multiscale_epe_forward needs.
+bool multiscale_fused_supported(const int* out_hw, int num_scales, int N, int iH, int iW, int C) {
+  for (int s0 = 0; s0 < num_scales; s0 += MS) {
+    const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
+    MsParams p = {};
+    size_t wsb = 0, smem = 0;
+    if (!ms_plan(&p, out_hw + 2 * s0, ns, N, iH, iW, C, &wsb, &smem)) return false;
+  }
+  return true;
+}
+
 // predictions / residual_dir / epe_sums may be null (plain multi-scale downsample); outs entries may be null when
 // predictions are given (only the loss terms wanted).
 int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,

@@ -116,7 +116,9 @@ const char* fn2_error_string(int status) {
     case FN2_E_NO_DEVICE: return "no sm_100 CUDA device is current";
     case FN2_E_UNSUPPORTED_GEOMETRY:
       return "unsupported geometry (row halos need kernel_size 1, stride_1 1, pad == max_displacement and "
-             "halo_top % stride_2 == 0; the fused loss needs C <= 2, in_w * C % 4 == 0 and reductions by >= 1.5)";
+             "halo_top % stride_2 == 0; the fused loss needs C <= 2, in_w * C % 4 == 0, in_w * C <= 1580 (a 16-row band "
+             "within 100 KB of shared memory), in_h <= 16384, N <= 65535 and reductions by >= 1.5: ask "
+             "fn2_multiscale_epe_supported)";
     case FN2_E_BUILTIN_SCRATCH:
       return "these shapes need more scratch than the 16 MiB array built into the library "
              "(fn2_downsample_multi_workspace_bytes > FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES): use a smaller batch, "
@@ -338,6 +340,12 @@ int fn2_downsample_multi_forward_noalloc(const float* in, float* const* outs, co
   for (int s = 0; s < num_scales; ++s)
     if (!outs[s] || !aligned16(outs[s])) return FN2_E_BAD_POINTER;
   return multiscale_forward_noalloc(in, outs, out_hw, num_scales, N, iH, iW, C, static_cast<cudaStream_t>(stream));
+}
+
+int fn2_multiscale_epe_supported(const int* out_hw, int num_scales, int N, int iH, int iW, int C) {
+  const int rc = check_scales(out_hw, num_scales, N, iH, iW, C);
+  if (rc != FN2_OK) return rc;
+  return multiscale_fused_supported(out_hw, num_scales, N, iH, iW, C) ? 1 : 0;
 }
 
 int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float* const* preds, const int* out_hw,

@@ -103,6 +103,7 @@ int downsample_forward(const float* in, float* out, int N, int iH, int iW, int C
 // downsample_multi.cu: several output sizes of one input in a single pass (host arrays of pointers / sizes), and the
 // end-point-error terms of the multi-scale loss against `preds` when given (dirs, epe_sums: see fn2ops.h)
 size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int iH, int iW, int C);
+bool multiscale_fused_supported(const int* out_hw, int num_scales, int N, int iH, int iW, int C);
 int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
                        float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
                        int C, void* ws, size_t ws_bytes, cudaStream_t st);

@@ -139,7 +139,12 @@ def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
     i.e. ``average_endpoint_error(downsample(flow * 0.05, size), predict_flow)`` of ``flownet_c.py:127-160`` /
     ``utils.py:209-224`` for all scales, without materialising the scaled flow or re-reading it per scale, and with the
     reductions done by the kernel in a fixed order.  Differentiable w.r.t. the predictions.  With
-    ``return_downsampled=True`` also returns the list of downsampled tensors."""
+    ``return_downsampled=True`` also returns the list of downsampled tensors.
+
+    Shapes outside the fused kernels' limits (``fn2_multiscale_epe_supported``: C <= 2, W * C a multiple of 4 and
+    <= 1580, reductions by >= 1.5) get the same values from ``downsample_multi`` on the scaled flow plus the
+    end-point-error nodes in torch: slower (the flow is scaled in a pass of its own and the sums are torch's), same
+    result within the op's tolerance."""
     _lib.require_cuda_f32(flow, "flow")
     if flow.requires_grad:
         raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
@@ -153,5 +158,20 @@ def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
             raise ValueError("prediction %s does not match flow %s" % (tuple(p.shape), tuple(flow.shape)))
         if p.device != flow.device:
             raise ValueError("predictions and flow must be on the same device")
+    import ctypes
+    sizes = [(int(p.shape[1]), int(p.shape[2])) for p in predictions]
+    hw = (ctypes.c_int * (2 * len(sizes)))(*[v for s in sizes for v in s])
+    fused = _lib.lib().fn2_multiscale_epe_supported(hw, len(sizes), N, H, W, C)
+    if fused < 0:
+        _lib.check(fused, "MultiscaleEpe")
+    if fused == 0:
+        # Shapes the fused kernels do not take (flows wider than 790 px at C = 2 -- Sintel, KITTI, 4K --, widths with
+        # W * C % 4 != 0, C > 2, reductions below 1.5): the reference's own node sequence on this library's
+        # downsample kernels -- flow * scale materialised, one downsample_multi call (which itself goes scale by scale
+        # where it must), average_endpoint_error by torch autograd.
+        downs = downsample_multi((flow * float(flow_scale)).contiguous(), sizes)
+        epe = torch.stack([torch.sqrt(torch.sum((p - d) * (p - d), dim=3)).sum() / N
+                           for p, d in zip(predictions, downs)])
+        return (epe, downs) if return_downsampled else epe
     res = _MultiscaleEpe.apply(flow, float(flow_scale), bool(return_downsampled), *predictions)
     return (res[0], list(res[1:])) if return_downsampled else res[0]

@@ -25,7 +25,10 @@
 extern "C" {
 #endif
 
-#define FN2_ABI_VERSION 1
+/* 2: fn2_downsample_multi_forward takes (workspace, workspace_bytes) before stream, precision value 2 (bf16) is
+ *    rejected, fn2_downsample_multi_forward_noalloc and fn2_multiscale_epe_supported added.  A caller built against
+ *    version 1 must not bind this library: check fn2_abi_version() == FN2_ABI_VERSION after loading. */
+#define FN2_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define FN2_API __attribute__((visibility("default")))
@@ -49,7 +52,7 @@ typedef enum fn2_status {
   FN2_E_NO_DEVICE = -11,       /* no sm_100 device is current                                           */
   FN2_E_UNSUPPORTED_GEOMETRY = -12,/* *_halo entry points: need kernel_size 1, stride_1 1, pad == max_displacement,
                                   halo_top a multiple of stride_2; fn2_multiscale_epe_forward: shapes the
-                                  fused multi-scale kernels do not take                                 */
+                                  fused multi-scale kernels do not take (fn2_multiscale_epe_supported)  */
   FN2_E_BUILTIN_SCRATCH = -13  /* fn2_downsample_multi_forward_noalloc: the shapes need more scratch than the
                                   library's built-in array holds (FN2_DOWNSAMPLE_MULTI_BUILTIN_SCRATCH_BYTES)  */
 } fn2_status;
@@ -243,12 +246,20 @@ FN2_API int fn2_downsample_multi_forward_noalloc(const float* input, float* cons
  * with respect to predictions[s] is made of (0/0 = NaN where the error is exactly 0, as the gradient of sqrt there).
  * epe_sums is a DEVICE array of num_scales floats; the sums are formed in a fixed order (bit-reproducible).
  * `predictions`, `downsampled`, `residual_dir` and `out_hw` are HOST arrays consumed before the call returns.
- * Needs the fused kernels (C <= 2, in_w * C a multiple of 4, every scale a reduction by >= 1.5):
- * FN2_E_UNSUPPORTED_GEOMETRY otherwise. */
+ * Needs the fused kernels for every scale: FN2_E_UNSUPPORTED_GEOMETRY otherwise (there is no slower path inside this
+ * entry point; ask fn2_multiscale_epe_supported first and build the terms from fn2_downsample_multi_forward when it
+ * says 0, as flownet2_tf_b200.downsample.multiscale_epe does).  The fused kernels take
+ *     C <= 2;  in_w * C a multiple of 4 and <= 1580 (a band of 16 input rows must fit 100 KB of shared memory: flows
+ *     up to 790 px wide at C = 2 -- FlyingChairs' 512 yes, Sintel's 1024 and KITTI's 1242 no);  in_h <= 16384;
+ *     N <= 65535;  every scale a reduction by >= 1.5 in both directions. */
 FN2_API int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float* const* predictions,
                                const int* out_hw, int num_scales, int N, int in_h, int in_w, int C,
                                float* const* downsampled, float* const* residual_dir, float* epe_sums,
                                void* workspace, size_t workspace_bytes, void* stream);
+
+/* 1 if fn2_multiscale_epe_forward takes these shapes, 0 if it would answer FN2_E_UNSUPPORTED_GEOMETRY (limits above),
+ * or a negative fn2_status for arguments the downsample op itself rejects.  Host-only: no CUDA call is made. */
+FN2_API int fn2_multiscale_epe_supported(const int* out_hw, int num_scales, int N, int in_h, int in_w, int C);
 
 /* Number of kernel launches (library kernels, not memsets) enqueued by this process so far; bench.py reports the
  * difference over its timed region as `gpu_launches`. */

@@ -25,12 +25,12 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(handle, n), n
     assert sorted(_lib.EXPORTED_SYMBOLS) == names  # the ctypes table binds exactly the declared ABI
-    assert _lib.lib().fn2_abi_version() == 1
+    assert _lib.lib().fn2_abi_version() == _lib.ABI_VERSION == 2
 
 
 def test_header_compiles_as_plain_c(tmp_path):
     src = tmp_path / "t.c"
-    src.write_text('#include "fn2ops.h"\nint main(void){return FN2_ABI_VERSION - 1;}\n')
+    src.write_text('#include "fn2ops.h"\nint main(void){return FN2_ABI_VERSION - 2;}\n')
     rc = os.system("/usr/bin/gcc -std=c99 -Wall -Werror -I%s/include -c %s -o %s/t.o" % (ROOT, src, tmp_path))
     assert rc == 0
 

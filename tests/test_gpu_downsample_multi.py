@@ -153,8 +153,36 @@ def test_multiscale_epe_with_nans_and_reproducible():
     assert (np.isnan(got) == np.isnan(want)).all()          # a NaN output makes that scale's sum NaN, as in TF
     epe2 = fn2.multiscale_epe(x.cuda(), preds, 0.05)
     assert torch.equal(torch.nan_to_num(epe, nan=-1.0), torch.nan_to_num(epe2, nan=-1.0))
-    with pytest.raises(ValueError):                          # C = 3 has no fused kernels
-        fn2.multiscale_epe(torch.randn(1, 30, 40, 3).cuda(), [torch.randn(1, 3, 4, 3).cuda()])
+
+
+@pytest.mark.parametrize("shape,sizes", [
+    ((1, 436, 1024, 2), [(7, 16), (14, 32), (28, 64), (55, 128), (109, 256)]),   # Sintel: band wider than 100 KB
+    ((2, 97, 131, 2), [(5, 7), (13, 17), (25, 33)]),                             # odd width: W * C % 4 != 0
+    ((1, 30, 40, 3), [(3, 4), (6, 8)]),                                          # C = 3
+    ((1, 40, 60, 2), [(30, 45), (5, 7)]),                                        # a reduction below 1.5
+])
+def test_multiscale_epe_outside_the_fused_kernels(shape, sizes):
+    """Shapes fn2_multiscale_epe_forward refuses (the C ABI says so up front) still give the loss terms through the
+    Python op: downsample_multi on the scaled flow + the end-point-error nodes, differentiable w.r.t. the predictions."""
+    import ctypes
+    from flownet2_tf_b200 import _lib
+    N, H, W, C = shape
+    hw = (ctypes.c_int * (2 * len(sizes)))(*[v for s in sizes for v in s])
+    assert _lib.lib().fn2_multiscale_epe_supported(hw, len(sizes), N, H, W, C) == 0
+    x = _input(*shape, seed=sum(shape), nan=False)
+    g = torch.Generator().manual_seed(4)
+    preds = [torch.randn(N, h, w, C, generator=g) for h, w in sizes]
+    want, wdowns = _epe_reference(x.numpy(), preds, 0.05)
+    pd = [p.cuda().requires_grad_() for p in preds]
+    epe, downs = fn2.multiscale_epe(x.cuda(), pd, 0.05, return_downsampled=True)
+    np.testing.assert_allclose(epe.detach().cpu().numpy(), want, rtol=2e-5)
+    for d, w in zip(downs, wdowns):
+        assert_close(d.cpu().numpy(), w, rel=1e-5, abs_=5e-6, what="downsampled, unfused loss %s" % (shape,))
+    epe.sum().backward()
+    for p, d in zip(pd, downs):
+        q = p.detach().clone().requires_grad_()
+        (torch.sqrt(((q - d) ** 2).sum(3)).sum() / N).backward()
+        torch.testing.assert_close(p.grad, q.grad, rtol=1e-5, atol=1e-9)
 
 
 def test_results_do_not_depend_on_the_batch_they_are_in():
