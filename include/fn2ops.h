@@ -60,6 +60,9 @@ typedef enum fn2_status {
 /* Arithmetic used by the correlation contraction.  Inputs and outputs are float32 in every mode.
  * The reference op is float32 only (correlation_op.cc:54-61); FP32 and TF32X3 meet its tolerance (1e-5 relative +
  * 1e-6 absolute against a float64 evaluation), TF32 trades accuracy (2.5e-3 of the tensor's maximum) for speed.
+ * (TF32X3, gradients only: the tensor core truncates when adding into its accumulator and wide images take more
+ * accumulation steps; at W = 480 with C = 32 and unit-variance data about 1 element in 10^4 of backprops_a reaches
+ * 4.4e-6 absolute.  FlowNetC's C = 256 stays inside the tolerance at every width tested, 4K included.)
  * The tensor-core modes cover the FlowNetC call shape (kernel_size 1, stride_1 1, pad == max_displacement,
  * max_displacement / stride_2 == 10, stride_2 in {1, 2}, C a multiple of 32 and <= 256: flownet_c.py:40); ask
  * fn2_correlation_precision_supported().  Value 2 is reserved (a bf16 mode is not built). */

@@ -16,10 +16,10 @@ ARGS = (1, 20, 1, 2, 20)
 TF32_TOL = 2.5e-3
 
 
-def _check(got, want, precision, what):
+def _check(got, want, precision, what, abs_=1e-6):
     got = got.detach().cpu().numpy().astype(np.float64)
-    if precision == "fp32":
-        assert_close(got, want, what=what)
+    if precision != "tf32":   # fp32, split-tf32 and the default (None): the reference's tolerance, elementwise
+        assert_close(got, want, abs_=abs_, what=what)
     else:
         err = np.abs(got - want).max() / max(np.abs(want).max(), 1e-30)
         assert err <= TF32_TOL, "%s: %.3e of max" % (what, err)
@@ -55,9 +55,20 @@ def test_wide_exact_on_integer_inputs():
     np.testing.assert_array_equal(gb.cpu().numpy().astype(np.float64), wgb)
 
 
-@pytest.mark.parametrize("precision", ["fp32", "tf32"])
-@pytest.mark.parametrize("world,H,W,C", [(2, 44, 40, 32), (3, 70, 90, 64), (4, 96, 24, 32)])
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "tf32x3", None])
+@pytest.mark.parametrize("world,H,W,C", [(2, 44, 40, 32), (3, 70, 90, 64), (4, 96, 24, 32),
+                                         (4, 136, 480, 256),   # the 4K conv3 width and depth, 34-row strips (8 GPUs')
+                                         (4, 136, 480, 32)])   # the same width with few channels: see below
 def test_strips_match_whole_image(precision, world, H, W, C):
+    """None = what correlation_strips and bench.py's strips4k leg run by default (split-tf32 where covered).
+
+    Known limit, pinned here: the split-tf32 BACKWARD on a wide image with few channels.  The tensor core truncates
+    when it adds into its fp32 accumulator, the banded-Gram backward takes more accumulation steps the wider the
+    column class, and with C = 32 the 1/C normalisation leaves the sums 8x larger than at C = 256 against the same
+    absolute bound: at W = 480, C = 32, unit-variance gradients, about 1 element in 10^4 of backprops_a misses
+    1e-6 + 1e-5 |x| (largest error 4.4e-6).  That case is held to 8e-6 + 1e-5 |x|; at the 4K shape's C = 256 the
+    reference's own tolerance holds.  precision="fp32" is exact-tolerance everywhere."""
+    grad_abs = 8e-6 if (precision in ("tf32x3", None) and W >= 480 and C < 128) else 1e-6
     a, b = corr_inputs(1, H, W, C)
     g = grad_like((1, H, W, 441))
     want = o.c_correlation(a.numpy(), b.numpy(), *ARGS, f64=True)
@@ -78,8 +89,8 @@ def test_strips_match_whole_image(precision, world, H, W, C):
         ga[:, y0:y1] = ga_s.cpu()
         gb[:, y0 - top:y1 + bottom] += gb_ext.cpu()      # what the mirror exchange + add does
     _check(out, want, precision, "forward")
-    _check(ga, wga, precision, "backprops_a")
-    _check(gb, wgb, precision, "backprops_b")
+    _check(ga, wga, precision, "backprops_a", abs_=grad_abs)
+    _check(gb, wgb, precision, "backprops_b", abs_=grad_abs)
 
 
 def test_halo_entry_points_reject_other_geometries():
@@ -110,3 +121,27 @@ def test_nccl_strips_on_two_gpus_match_the_whole_op():
     assert res.returncode == 0, res.stderr[-2000:]
     line = json.loads([l for l in res.stdout.splitlines() if l.startswith("{")][-1])
     assert line["gpus"] == 2 and line["max_rel_err_vs_whole_op"] <= 2e-3
+
+
+@pytest.mark.parametrize("precision,min_rows", [("default", 100), ("default", 0), ("tf32x3", 0), ("tf32", 0),
+                                                ("fp32", 0)])
+def test_nccl_strips_match_the_oracle(precision, min_rows):
+    """The strips over real NCCL (two GPUs) against the float64 CPU oracle of the whole image, in the precision the
+    strips4k bench leg runs ("default" = split-tf32) and with either schedule: exchange first (strips under
+    FN2_STRIPS_OVERLAP_MIN_ROWS) or exchange overlapped with the interior rows (min_rows 0).  Worker:
+    tests/_strips_nccl_worker.py."""
+    import json
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, FN2_STRIPS_OVERLAP_MIN_ROWS=str(min_rows))
+    res = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29534",
+                          os.path.join(here, "_strips_nccl_worker.py"), precision, "48", "96", "64"],
+                         capture_output=True, text=True, timeout=600, env=env)
+    assert res.returncode == 0, (res.stdout[-1500:], res.stderr[-2500:])
+    line = json.loads([l for l in res.stdout.splitlines() if l.startswith("{")][-1])
+    assert line["gpus"] == 2 and line["overlap"] == (min_rows == 0)
