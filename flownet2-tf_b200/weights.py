@@ -18,6 +18,7 @@ Going back to PyTorch: conv ``(h, w, in, out) -> (out, in, h, w)`` and transpose
 (in, out, h, w)`` are both ``transpose(3, 2, 0, 1)``.
 """
 import os
+import pickle
 import struct
 
 import numpy as np
@@ -120,9 +121,50 @@ def variables_from_state_dict(model):
 
 
 # ------------------------------------------------------------------------------------------------ Caffe-npy
-def load_npy(path):
-    """The pickled dict written by ``convert_caffe_weights_to_npy.py:497`` (``np.save(path, dict)``)."""
-    obj = np.load(path, allow_pickle=True)
+_NPY_PICKLE_GLOBALS = {   # all that a pickled {name: ndarray} dict needs, under numpy 1.x and 2.x module paths
+    ("numpy.core.multiarray", "_reconstruct"), ("numpy._core.multiarray", "_reconstruct"),
+    ("numpy.core.multiarray", "scalar"), ("numpy._core.multiarray", "scalar"),
+    ("numpy", "ndarray"), ("numpy", "dtype"), ("_codecs", "encode"), ("collections", "OrderedDict"),
+}
+
+
+class _ArraysOnlyUnpickler(pickle.Unpickler):
+    """pickle.Unpickler that resolves nothing but the constructors of numpy arrays, dtypes and scalars."""
+
+    def find_class(self, module, name):
+        if (module, name) in _NPY_PICKLE_GLOBALS:
+            return super().find_class(module, name)
+        raise pickle.UnpicklingError(
+            "weights file asks for %s.%s: not a plain {name: array} dict (refused; pass trusted=True only for a file "
+            "whose origin you trust)" % (module, name))
+
+
+def load_npy(path, trusted=False):
+    """The pickled dict written by ``convert_caffe_weights_to_npy.py:497`` (``np.save(path, dict)``).
+
+    That format IS a pickle: ``np.load(allow_pickle=True)`` on a downloaded weights file would run whatever code the
+    file names.  By default the file is therefore read with an unpickler that only admits numpy arrays, dtypes and
+    scalars inside builtin containers, which is all the reference's converter writes; anything else is refused.
+    ``trusted=True`` hands the file to ``np.load(allow_pickle=True)`` as the reference does -- arbitrary code execution
+    if the file is hostile.  ``convert_npy_to_npz`` rewrites a file once into a pickle-free ``.npz``."""
+    if trusted:
+        obj = np.load(path, allow_pickle=True)
+    else:
+        with open(path, "rb") as f:
+            version = np.lib.format.read_magic(f)
+            if version == (1, 0):
+                _, _, dtype = np.lib.format.read_array_header_1_0(f)
+            else:
+                _, _, dtype = np.lib.format.read_array_header_2_0(f)
+            if not dtype.hasobject:
+                raise ValueError("%s does not hold a {name: array} dict" % path)
+            try:
+                obj = _ArraysOnlyUnpickler(f).load()
+            except UnicodeError:      # written by Python 2 (the Caffe tool chain): 8-bit strings
+                f.seek(0)
+                np.lib.format.read_magic(f)
+                (np.lib.format.read_array_header_1_0 if version == (1, 0) else np.lib.format.read_array_header_2_0)(f)
+                obj = _ArraysOnlyUnpickler(f, encoding="latin1").load()
     if isinstance(obj, np.ndarray) and obj.dtype == object and obj.shape == ():
         obj = obj.item()
     if not isinstance(obj, dict):
@@ -130,13 +172,26 @@ def load_npy(path):
     return {str(k): np.asarray(v) for k, v in obj.items()}
 
 
+def convert_npy_to_npz(path, out_path, trusted=False):
+    """Rewrites the pickled dict as a plain ``.npz`` archive (no pickle inside); ``load_npz`` reads it back."""
+    np.savez(out_path, **load_npy(path, trusted=trusted))
+
+
+def load_npz(path):
+    with np.load(path, allow_pickle=False) as z:
+        return {k: z[k] for k in z.files}
+
+
 def save_npy(path, variables):
     with open(path, "wb") as f:   # a file object: np.save would otherwise append ".npy"
         np.save(f, dict(variables), allow_pickle=True)
 
 
-def load_npy_into(model, path, strict=True, prefix_map=None):
-    model.load_state_dict(state_dict_from_variables(model, load_npy(path), strict, prefix_map), strict=strict)
+def load_npy_into(model, path, strict=True, prefix_map=None, trusted=False):
+    """``path``: the reference's pickled ``.npy`` dict (read with the arrays-only unpickler unless ``trusted``; see
+    ``load_npy``) or a ``.npz`` written by ``convert_npy_to_npz``."""
+    variables = load_npz(path) if str(path).endswith(".npz") else load_npy(path, trusted=trusted)
+    model.load_state_dict(state_dict_from_variables(model, variables, strict, prefix_map), strict=strict)
     return model
 
 
@@ -412,8 +467,11 @@ def _field(num, wt, payload):
 
 
 def save_tf_checkpoint(prefix, variables, global_step=None):
-    """Writes ``{name: array}`` as a one-shard V2 checkpoint readable by ``tf.train.Saver`` /
-    ``slim.assign_from_checkpoint`` (and by ``load_tf_checkpoint``).  ``global_step`` adds the int64 scalar the
+    """Writes ``{name: array}`` as a one-shard V2 checkpoint in the layout ``tf.train.Saver`` /
+    ``slim.assign_from_checkpoint`` read (and ``load_tf_checkpoint`` reads back).  TensorFlow-side compatibility is
+    UNTESTED: there is no TensorFlow in this image and no TF-written checkpoint under the reference tree, so nothing
+    here has been read by TensorFlow, and the reader has only seen files built to the published format (this writer,
+    and the hand-built prefix-compressed and snappy blocks of tests/test_weights.py).  ``global_step`` adds the int64 scalar the
     reference's training loop expects (``net.py:1443`` parses the step from the file name as well)."""
     items = {k: np.ascontiguousarray(v) for k, v in variables.items()}
     if global_step is not None:
