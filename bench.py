@@ -15,8 +15,10 @@ metric = image pairs / s (whole job, all GPUs; batch-sharded, no collective on t
 Prints ONE JSON line on rank 0.  The headline runs the correlation at the drop-in default precision ("auto" =
 split-tf32, which meets the reference's float32 tolerance); `per_precision` carries the other modes.  Extra keys:
 `cfg1` (one pair, warm and cold L2), `cfg2` (batch-8 warp + downsample), `reference_gpu_kernels` (the reference's own
-CUDA kernels on this GPU, per op), `e2e_copy_ceiling`, and with N > 1 `strips4k` (BASELINE config 5: the 4K
-correlation cut into row strips, NCCL halo exchange inside the timed region; also `--config strips4k` on its own).
+CUDA kernels on this GPU, per op), `e2e_copy_ceiling`, `cfg3` / `cfg4` (FlowNetC training step and FlowNet2 stacked
+inference through flownet2_tf_b200.graphs, 8 pairs per GPU; also `--config flownetc_train | flownet2_infer`), and
+`strips4k` (BASELINE config 5: the 4K correlation cut into N row strips, NCCL halo exchange inside the timed region;
+N = 1 is the whole pair on one GPU, the strong-scaling denominator; also `--config strips4k` on its own).
 `--impl reference` times the CPU restatement of the reference ops (the reference has no CPU implementation of these
 ops and its TF GPU ops cannot be built here) on all host threads.
 """
@@ -713,12 +715,28 @@ def main():
         del live, dev_in
 
     # ---- config 5 inside the default multi-GPU run, so that the scaling run records a data-path collective ----
+    # (N = 1 gives the strong-scaling denominator: the whole 4K pair on one GPU, no exchange)
     strips4k = None
-    if world > 1 and not args.no_extras:
+    if not args.no_extras:
         try:
             strips4k = strips_bench(torch, dist, fn2, dev, rank, world, precision, 20, 3, hbm_peak)
         except Exception as exc:  # pragma: no cover
             strips4k = {"unavailable": str(exc)[:300]}
+
+    # ---- configs 3 and 4 (the callers of the path) on every N, after the hot path's own timed region ------------
+    cfg3 = cfg4 = None
+    if not args.no_extras:
+        for name in ("flownetc_train", "flownet2_infer"):
+            try:
+                res = graphs_bench(torch, dist, dev, rank, world, precision, name, 10, 3, 8)
+                res = {k: res[k] for k in ("value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "config",
+                                           "finite", "launch")}
+            except Exception as exc:  # pragma: no cover
+                res = {"unavailable": str(exc)[:300]}
+            if name == "flownetc_train":
+                cfg3 = res
+            else:
+                cfg4 = res
 
     if rank != 0:
         if world > 1:
@@ -912,7 +930,8 @@ def main():
         "launch": "CUDA graph replay per op, 5 per step" if graphs else "eager launches",
         "clocks": clocks, "e2e": e2e, "e2e_copy_ceiling": ceiling,
         "gpu_launches": int(launches), "roofline": roofline, "per_op": per_op, "per_precision": per_precision,
-        "cpu_baseline": cpu, "cfg1": cfg1, "cfg2": cfg2, "strips4k": strips4k, "reference_gpu_kernels": ref_gpu,
+        "cpu_baseline": cpu, "cfg1": cfg1, "cfg2": cfg2, "cfg3": cfg3, "cfg4": cfg4,
+        "strips4k": strips4k, "reference_gpu_kernels": ref_gpu,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

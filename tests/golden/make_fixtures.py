@@ -1,8 +1,9 @@
-"""Packs the reference's own sample pair 0 into tests/golden/sample0.npz (inputs only; ~0.5 MB compressed):
+"""Packs the reference's own sample pairs into tests/golden/sample0.npz and sample1.npz (inputs only; ~0.5 MB each,
+compressed); for pair K:
 
-    image  uint8  [384,512,3]   /root/reference/data/samples/0img1.ppm   (the image FlowNet2 warps, flownet_cs.py:24)
-    image0 uint8  [384,512,3]   /root/reference/data/samples/0img0.ppm   (the reference image of the brightness error)
-    flow   float32 [384,512,2]  /root/reference/data/samples/0flow.flo   (ground truth, flows down to -108.9 px)
+    image  uint8  [384,512,3]   /root/reference/data/samples/Kimg1.ppm   (the image FlowNet2 warps, flownet_cs.py:24)
+    image0 uint8  [384,512,3]   /root/reference/data/samples/Kimg0.ppm   (the reference image of the brightness error)
+    flow   float32 [384,512,2]  /root/reference/data/samples/Kflow.flo   (ground truth; pair 0: flows down to -108.9 px)
 
 Run where /root/reference exists:  python tests/golden/make_fixtures.py
 The GPU tests (tests/test_gpu_fixtures.py) run the kernels on these real inputs against the oracle and, when built,
@@ -38,11 +39,12 @@ def read_ppm(path):
 
 def main():
     from flownet2_tf_b200.flo import read_flo
-    out = os.path.join(ROOT, "tests", "golden", "sample0.npz")
-    np.savez_compressed(out, image=read_ppm(os.path.join(SAMPLES, "0img1.ppm")),
-                        image0=read_ppm(os.path.join(SAMPLES, "0img0.ppm")),
-                        flow=read_flo(os.path.join(SAMPLES, "0flow.flo")))
-    print("wrote", out, os.path.getsize(out), "bytes")
+    for k in (0, 1):
+        out = os.path.join(ROOT, "tests", "golden", "sample%d.npz" % k)
+        np.savez_compressed(out, image=read_ppm(os.path.join(SAMPLES, "%dimg1.ppm" % k)),
+                            image0=read_ppm(os.path.join(SAMPLES, "%dimg0.ppm" % k)),
+                            flow=read_flo(os.path.join(SAMPLES, "%dflow.flo" % k)))
+        print("wrote", out, os.path.getsize(out), "bytes")
 
 
 if __name__ == "__main__":

@@ -77,13 +77,14 @@ def test_cuda_reproduces_reference_warp_and_downsample():
             assert_close(fn2.downsample(x, size).cpu().numpy(), z[key], rel=1e-5, abs_=5e-6, what=key)
 
 
-def test_both_oracles_agree_on_the_reference_sample_pair():
-    """tests/golden/sample0.npz = the reference's data/samples pair 0 (made by tests/golden/make_fixtures.py): the C
+@pytest.mark.parametrize("name,flow_min", [("sample0.npz", -108.90625), ("sample1.npz", -37.6875)])
+def test_both_oracles_agree_on_the_reference_sample_pair(name, flow_min):
+    """tests/golden/sampleK.npz = the reference's data/samples pair K (made by tests/golden/make_fixtures.py): the C
     restatement and the independent float64 numpy restatement give the same warp, gradients and downsampled flow on
     real data (smooth flows, displacements down to -108.9 px, pixel values 0..255)."""
-    z = np.load(os.path.join(GOLD, "sample0.npz"))
+    z = np.load(os.path.join(GOLD, name))
     assert z["image"].shape == (384, 512, 3) and z["flow"].shape == (384, 512, 2)
-    assert float(z["flow"].min()) == -108.90625
+    assert float(z["flow"].min()) == flow_min
     image = z["image"].astype(np.float32)[None, 100:228, 200:392]
     flow = np.ascontiguousarray(z["flow"][None, 100:228, 200:392])
     assert_close(o.c_flow_warp(image, flow), o.np_flow_warp(image, flow), rel=1e-5, abs_=1e-4, what="warp")

@@ -1,5 +1,5 @@
-"""GPU parity on the reference's REAL sample pair (tests/golden/sample0.npz = data/samples/0img1.ppm, 0img0.ppm,
-0flow.flo, packed by tests/golden/make_fixtures.py): flow_warp forward / backward and all five loss scales of
+"""GPU parity on the reference's REAL sample pairs (tests/golden/sampleK.npz = data/samples/Kimg1.ppm, Kimg0.ppm,
+Kflow.flo for K = 0 and 1, packed by tests/golden/make_fixtures.py; every test runs on both): flow_warp forward / backward and all five loss scales of
 downsample on the ground-truth flow (SURVEY.md section 8 c/d), against the oracle and, when built, against the
 reference's own kernels.  Real flows are smooth with large displacements (down to -108.9 px): neighbouring pixels share
 taps, many taps leave the staged window -- the opposite regime of the synthetic iid flows of the other tests."""
@@ -18,12 +18,12 @@ from oracle import oracle as o  # noqa: E402
 from oracle import ref  # noqa: E402
 
 LOSS_SIZES = [(6, 8), (12, 16), (24, 32), (48, 64), (96, 128)]   # flownet_c.py:135-160
-FIX = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sample0.npz")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-@pytest.fixture(scope="module")
-def sample():
-    z = np.load(FIX)
+@pytest.fixture(scope="module", params=["sample0.npz", "sample1.npz"])
+def sample(request):
+    z = np.load(os.path.join(GOLD, request.param))
     image = torch.from_numpy(z["image"].astype(np.float32))[None].contiguous()     # [1,384,512,3], 0..255 as the
     image0 = torch.from_numpy(z["image0"].astype(np.float32))[None].contiguous()   # reference feeds it (net.py:301)
     flow = torch.from_numpy(z["flow"])[None].contiguous()
