@@ -50,6 +50,10 @@ _SIGNATURES = {
     "fn2_downsample_multi_forward_noalloc": (c_int, [c_void_p, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)]
                                              + [c_int] * 5 + [c_void_p]),
     "fn2_downsample_multi_workspace_bytes": (c_size_t, [ctypes.POINTER(c_int)] + [c_int] * 5),
+    "fn2_multiscale_epe_edges_forward": (c_int, [c_void_p, ctypes.c_float, ctypes.POINTER(c_void_p),
+                                                 ctypes.POINTER(c_void_p), ctypes.c_float, ctypes.POINTER(c_int)]
+                                         + [c_int] * 5 + [ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p), c_void_p,
+                                                          c_void_p, c_size_t, c_void_p]),
     "fn2_multiscale_epe_supported": (c_int, [ctypes.POINTER(c_int)] + [c_int] * 5),
     "fn2_multiscale_epe_forward": (c_int, [c_void_p, ctypes.c_float, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int)]
                                    + [c_int] * 5 + [ctypes.POINTER(c_void_p), ctypes.POINTER(c_void_p), c_void_p,

@@ -74,6 +74,8 @@ struct MsParams {
   const float* pred[MS];          // predictions to compare with (null: plain downsample)
   float* dir[MS];                 // (pred - down) / epe per element (may be null)
   float* epe;                     // [ns] per-scale sum of end-point errors, divided by N (null without pred)
+  const float* edge[MS];          // HFEM 'edges' loss: [N,oH,oW,1] edge map of scale s (null: plain EPE), and its
+  float lambda_w;                 // weight: every pixel's error counts (1 + lambda_w * edge) times (utils.py:326-334)
   size_t ctrlOff, partOff;        // byte offsets in the workspace: control block (ticket + block sums), partials
 };
 
@@ -428,10 +430,16 @@ __global__ void __launch_bounds__(CB) ms_combine_kernel(MsParams p, float* __res
     }
     if (p.pred[s]) {
       epe = sqrtf(e2);                                       // utils.py:219-223
+      // HFEM 'edges' (utils.py:326-334): epe + lambda * (epe * edges) per pixel, each product rounded as the graph's
+      // separate nodes round it; the gradient w.r.t. the prediction carries the factor 1 + lambda * edges
+      const float edge = p.edge[s] ? __ldg(p.edge[s] + ((size_t)n * oH + dy) * oW + dx) : 0.f;
       if (p.dir[s]) {
+        const float w = fmaf(p.lambda_w, edge, 1.0f);
 #pragma unroll
-        for (int c = 0; c < CT; ++c) p.dir[s][o + c] = diff[c] / epe;   // 0/0 = NaN, as the gradient of sqrt at 0
+        for (int c = 0; c < CT; ++c)                          // 0/0 = NaN, as the gradient of sqrt at 0
+          p.dir[s][o + c] = p.edge[s] ? diff[c] / epe * w : diff[c] / epe;
       }
+      if (p.edge[s]) epe = __fadd_rn(epe, __fmul_rn(p.lambda_w, __fmul_rn(epe, edge)));
     }
   }
   if (p.epe == nullptr) return;                              // uniform: plain downsample
@@ -584,7 +592,7 @@ bool multiscale_fused_supported(const int* out_hw, int num_scales, int N, int iH
 // predictions are given (only the loss terms wanted).
 int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
                        float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
-                       int C, void* ws, size_t ws_bytes, cudaStream_t st) {
+                       int C, void* ws, size_t ws_bytes, cudaStream_t st, const float* const* edges, float lambda_w) {
   for (int s0 = 0; s0 < num_scales; s0 += MS) {
     const int ns = num_scales - s0 < MS ? num_scales - s0 : MS;
     MsParams p = {};
@@ -606,7 +614,9 @@ int multiscale_forward(const float* in, float in_scale, float* const* outs, cons
       p.out[s] = outs ? outs[s0 + s] : nullptr;
       p.pred[s] = preds ? preds[s0 + s] : nullptr;
       p.dir[s] = dirs ? dirs[s0 + s] : nullptr;
+      p.edge[s] = (preds && edges) ? edges[s0 + s] : nullptr;
     }
+    p.lambda_w = lambda_w;
     p.epe = preds ? epe_sums + s0 : nullptr;
     const int rc = C == 2 ? ms_launch<2>(p, smem, in, ws, st) : ms_launch<1>(p, smem, in, ws, st);
     if (rc != FN2_OK) return rc;

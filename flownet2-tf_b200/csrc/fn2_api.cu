@@ -365,4 +365,23 @@ int fn2_multiscale_epe_forward(const float* flow, float flow_scale, const float*
                             C, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int fn2_multiscale_epe_edges_forward(const float* flow, float flow_scale, const float* const* preds,
+                                     const float* const* edges, float lambda_w, const int* out_hw, int num_scales,
+                                     int N, int iH, int iW, int C, float* const* downsampled,
+                                     float* const* residual_dir, float* epe_sums, void* ws, size_t ws_bytes,
+                                     void* stream) {
+  const int rc = check_scales(out_hw, num_scales, N, iH, iW, C);
+  if (rc != FN2_OK) return rc;
+  if (!(flow_scale == flow_scale) || !(lambda_w == lambda_w)) return FN2_E_BAD_PARAM;
+  if (!flow || !preds || !edges || !epe_sums || !aligned16(flow)) return FN2_E_BAD_POINTER;
+  for (int s = 0; s < num_scales; ++s) {
+    if (!preds[s] || !aligned16(preds[s]) || !edges[s]) return FN2_E_BAD_POINTER;
+    if (downsampled && downsampled[s] && !aligned16(downsampled[s])) return FN2_E_BAD_POINTER;
+    if (residual_dir && residual_dir[s] && !aligned16(residual_dir[s])) return FN2_E_BAD_POINTER;
+  }
+  if (ws_bytes && (!ws || !aligned16(ws))) return FN2_E_BAD_POINTER;
+  return multiscale_forward(flow, flow_scale, downsampled, preds, residual_dir, epe_sums, out_hw, num_scales, N, iH, iW,
+                            C, ws, ws_bytes, static_cast<cudaStream_t>(stream), edges, lambda_w);
+}
+
 }  // extern "C"

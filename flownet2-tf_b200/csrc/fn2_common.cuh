@@ -106,7 +106,8 @@ size_t multiscale_workspace_bytes(const int* out_hw, int num_scales, int N, int 
 bool multiscale_fused_supported(const int* out_hw, int num_scales, int N, int iH, int iW, int C);
 int multiscale_forward(const float* in, float in_scale, float* const* outs, const float* const* preds,
                        float* const* dirs, float* epe_sums, const int* out_hw, int num_scales, int N, int iH, int iW,
-                       int C, void* ws, size_t ws_bytes, cudaStream_t st);
+                       int C, void* ws, size_t ws_bytes, cudaStream_t st, const float* const* edges = nullptr,
+                       float lambda_w = 0.f);
 // the plain multi-scale downsample with its scratch in the library's own device array (no workspace argument)
 int multiscale_forward_noalloc(const float* in, float* const* outs, const int* out_hw, int num_scales, int N, int iH,
                                int iW, int C, cudaStream_t st);

@@ -97,12 +97,12 @@ class _MultiscaleEpe(torch.autograd.Function):
     gradient needs); the ground-truth flow gets none, as in the reference (downsample has no registered gradient)."""
 
     @staticmethod
-    def forward(ctx, flow, scale, want_down, *preds):
+    def forward(ctx, flow, scale, want_down, edge_maps, lambda_w, *preds):
         import ctypes
         N, H, W, C = flow.shape
         sizes = [(int(p.shape[1]), int(p.shape[2])) for p in preds]
         k = len(preds)
-        need_grad = any(ctx.needs_input_grad[3:])
+        need_grad = any(ctx.needs_input_grad[5:])
         dirs = [torch.empty_like(p) for p in preds] if need_grad else []
         downs = [torch.empty_like(p) for p in preds] if want_down else []
         epe = torch.empty(k, dtype=torch.float32, device=flow.device)
@@ -113,9 +113,15 @@ class _MultiscaleEpe(torch.autograd.Function):
         hw = (ctypes.c_int * (2 * k))(*[v for s in sizes for v in s])
         with torch.cuda.device(flow.device):
             ws, nbytes, wsp = _multi_workspace(flow, hw, k)
-            st = _lib.lib().fn2_multiscale_epe_forward(flow.data_ptr(), float(scale), pp, hw, k, N, H, W, C, op, dp,
-                                                       epe.data_ptr(), wsp, nbytes,
-                                                       _lib.current_stream_ptr(flow.device))
+            if edge_maps is None:
+                st = _lib.lib().fn2_multiscale_epe_forward(flow.data_ptr(), float(scale), pp, hw, k, N, H, W, C, op, dp,
+                                                           epe.data_ptr(), wsp, nbytes,
+                                                           _lib.current_stream_ptr(flow.device))
+            else:
+                ep = arr(*[e.data_ptr() for e in edge_maps])
+                st = _lib.lib().fn2_multiscale_epe_edges_forward(flow.data_ptr(), float(scale), pp, ep, float(lambda_w),
+                                                                 hw, k, N, H, W, C, op, dp, epe.data_ptr(), wsp, nbytes,
+                                                                 _lib.current_stream_ptr(flow.device))
         _lib.check(st, "MultiscaleEpe")
         ctx.save_for_backward(*dirs)
         ctx.n, ctx.k = N, k
@@ -126,12 +132,12 @@ class _MultiscaleEpe(torch.autograd.Function):
     def backward(ctx, g_epe, *unused):
         dirs = ctx.saved_tensors
         if not dirs:
-            return (None,) * (3 + ctx.k)
-        grads = tuple((g_epe[s] / ctx.n) * d if ctx.needs_input_grad[3 + s] else None for s, d in enumerate(dirs))
-        return (None, None, None) + grads
+            return (None,) * (5 + ctx.k)
+        grads = tuple((g_epe[s] / ctx.n) * d if ctx.needs_input_grad[5 + s] else None for s, d in enumerate(dirs))
+        return (None,) * 5 + grads
 
 
-def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
+def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False, edges=None, lambda_w=2.0):
     """Per-scale data terms of the FlowNet training loss in ONE pass over ``flow``.
 
     For predictions p_s of shape [N,h_s,w_s,C] returns the tensor
@@ -140,6 +146,11 @@ def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
     ``utils.py:209-224`` for all scales, without materialising the scaled flow or re-reading it per scale, and with the
     reductions done by the kernel in a fixed order.  Differentiable w.r.t. the predictions.  With
     ``return_downsampled=True`` also returns the list of downsampled tensors.
+
+    ``edges`` ([N,H,W,1], values in [0,1]) switches on the edge weighting of the reference's HFEM loss in mode 'edges'
+    (``average_endpoint_error_hfem``, ``utils.py:326-334``; ``flownet_s_interp.py:170-239``): the map is downsampled
+    to every scale in one fused pass of its own and every pixel's error then counts ``1 + lambda_w * edges_s`` times,
+        epe[s] = sum_pixels (epe_s + lambda_w * epe_s * downsample(edges, size_s)) / N.
 
     Shapes outside the fused kernels' limits (``fn2_multiscale_epe_supported``: C <= 2, W * C a multiple of 4 and
     <= 1580, reductions by >= 1.5) get the same values from ``downsample_multi`` on the scaled flow plus the
@@ -160,6 +171,14 @@ def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
             raise ValueError("predictions and flow must be on the same device")
     import ctypes
     sizes = [(int(p.shape[1]), int(p.shape[2])) for p in predictions]
+    edge_maps = None
+    if edges is not None:
+        _lib.require_cuda_f32(edges, "edges")
+        if tuple(edges.shape) != (N, H, W, 1) or edges.device != flow.device:
+            raise ValueError("edges must be [N,H,W,1] on the flow's device, got %s" % (tuple(edges.shape),))
+        if edges.requires_grad:
+            raise LookupError("No gradient defined for operation 'Downsample' (the reference registers none)")
+        edge_maps = downsample_multi(edges, sizes)          # flownet_s_interp.py:177,191,205,219,233 in one pass
     hw = (ctypes.c_int * (2 * len(sizes)))(*[v for s in sizes for v in s])
     fused = _lib.lib().fn2_multiscale_epe_supported(hw, len(sizes), N, H, W, C)
     if fused < 0:
@@ -170,8 +189,11 @@ def multiscale_epe(flow, predictions, flow_scale=1.0, return_downsampled=False):
         # downsample kernels -- flow * scale materialised, one downsample_multi call (which itself goes scale by scale
         # where it must), average_endpoint_error by torch autograd.
         downs = downsample_multi((flow * float(flow_scale)).contiguous(), sizes)
-        epe = torch.stack([torch.sqrt(torch.sum((p - d) * (p - d), dim=3)).sum() / N
-                           for p, d in zip(predictions, downs)])
+        maps = [torch.sqrt(torch.sum((p - d) * (p - d), dim=3, keepdim=True)) for p, d in zip(predictions, downs)]
+        if edge_maps is not None:
+            maps = [m + float(lambda_w) * (m * e) for m, e in zip(maps, edge_maps)]
+        epe = torch.stack([m.sum() / N for m in maps])
         return (epe, downs) if return_downsampled else epe
-    res = _MultiscaleEpe.apply(flow, float(flow_scale), bool(return_downsampled), *predictions)
+    res = _MultiscaleEpe.apply(flow, float(flow_scale), bool(return_downsampled), edge_maps, float(lambda_w),
+                               *predictions)
     return (res[0], list(res[1:])) if return_downsampled else res[0]

@@ -419,6 +419,49 @@ def multiscale_loss(flow, predictions, ops, gt_scale=0.05, weights=LOSS_WEIGHTS)
     return weighted_loss(losses, weights), losses
 
 
+def average_endpoint_error_hfem(labels, predictions, add_hfem="", lambda_w=2.0, perc_hfem=50, edges=None):
+    """utils.py:227-339.  '' (or 'edges' without an edge map): the plain average end-point error.  'edges': every
+    pixel's error counts 1 + lambda_w * edges times (:326-334).  'hard': only the top perc_hfem per cent of the errors
+    count, (1 + lambda_w) times, rescaled by total / hard pixels (:268-324; the selection itself carries no
+    gradient, as tf.nn.top_k's indices)."""
+    n = predictions.shape[0]
+    d = predictions - labels
+    epe = torch.sqrt(torch.sum(d * d, dim=3, keepdim=True))
+    mode = (add_hfem or "").lower()
+    if mode == "hard":
+        flat = epe.reshape(-1)
+        k = int(round(float(perc_hfem) / 100.0 * flat.numel()))     # tf.round: half to even, as Python's round
+        top = torch.topk(flat, k).values
+        return (1.0 + lambda_w) * top.sum() / n * (flat.numel() / float(k))
+    if mode == "edges" and edges is not None:
+        return (epe + lambda_w * (epe * edges)).sum() / n
+    return epe.sum() / n
+
+
+def multiscale_loss_hfem(flow, predictions, ops, gt_scale=0.05, weights=LOSS_WEIGHTS, add_hfem="", lambda_w=2.0,
+                         perc_hfem=50, edges=None):
+    """The loss of the reference's HFEM variants (flownet_s_interp.py:160-245 and the other *_interp nets): as
+    ``multiscale_loss`` with ``average_endpoint_error_hfem`` per scale; in mode 'edges' the edge map [N,H,W,1] is
+    downsampled to every scale as well (:177,191,205,219,233).  With the library's ops the 'edges' mode is two fused
+    passes: all scales of the edge map, then flow scaling + downsampling + weighted error sums
+    (``ops.multiscale_epe(..., edges=)``, fn2_multiscale_epe_edges_forward)."""
+    preds = [predictions["predict_flow%d" % k] for k in (6, 5, 4, 3, 2)]
+    mode = (add_hfem or "").lower()
+    if mode not in ("hard", "edges") or (mode == "edges" and edges is None):
+        return multiscale_loss(flow, predictions, ops, gt_scale, weights)
+    if mode == "edges" and hasattr(ops, "multiscale_epe"):
+        epe = ops.multiscale_epe(flow.contiguous(), [p.contiguous() for p in preds], gt_scale,
+                                 edges=edges.contiguous(), lambda_w=lambda_w)
+        losses = [epe[i] for i in range(len(preds))]
+        return weighted_loss(losses, weights), losses
+    sizes = [(int(p.shape[1]), int(p.shape[2])) for p in preds]
+    many = getattr(ops, "downsample_multi", lambda x, ss: [ops.downsample(x, list(s)) for s in ss])
+    downs = many((flow * gt_scale).contiguous(), sizes)
+    emaps = many(edges.contiguous(), sizes) if mode == "edges" else [None] * len(preds)
+    losses = [average_endpoint_error_hfem(d, p, mode, lambda_w, perc_hfem, e) for d, p, e in zip(downs, preds, emaps)]
+    return weighted_loss(losses, weights), losses
+
+
 def l2_regularization(module, scale):
     """slim.l2_regularizer(scale) on the conv2d weights only (flownet_c.py:27-28; transposed convolutions and biases
     carry none): scale * sum(w^2) / 2, added by tf.losses.get_total_loss() (:166)."""

@@ -26,7 +26,8 @@ extern "C" {
 #endif
 
 /* 2: fn2_downsample_multi_forward takes (workspace, workspace_bytes) before stream, precision value 2 (bf16) is
- *    rejected, fn2_downsample_multi_forward_noalloc and fn2_multiscale_epe_supported added.  A caller built against
+ *    rejected; fn2_downsample_multi_forward_noalloc, fn2_multiscale_epe_supported and
+ *    fn2_multiscale_epe_edges_forward added.  A caller built against
  *    version 1 must not bind this library: check fn2_abi_version() == FN2_ABI_VERSION after loading. */
 #define FN2_ABI_VERSION 2
 
@@ -259,6 +260,22 @@ FN2_API int fn2_multiscale_epe_forward(const float* flow, float flow_scale, cons
                                const int* out_hw, int num_scales, int N, int in_h, int in_w, int C,
                                float* const* downsampled, float* const* residual_dir, float* epe_sums,
                                void* workspace, size_t workspace_bytes, void* stream);
+
+/* fn2_multiscale_epe_forward with the edge weighting of the reference's HFEM loss in mode 'edges'
+ * (average_endpoint_error_hfem, utils.py:227-339, branch :326-334; callers flownet_s_interp.py:170-239, which
+ * downsample the edge map to every scale first, :177,191,205,219,233):
+ *     epe_sums[s] = reduce_sum(epe_s + lambda_w * (epe_s * edges[s])) / N
+ * edges[s] is a device tensor [N,out_h,out_w,1] -- the edge map ALREADY downsampled to scale s (one
+ * fn2_downsample_multi_forward call on the [N,in_h,in_w,1] map gives all of them); `edges` itself is a HOST array like
+ * `predictions`.  residual_dir[s] then holds (1 + lambda_w * edges[s]) * (predictions[s] - flow_s) / epe_s, again the
+ * whole factor of the gradient with respect to predictions[s].  Everything else as fn2_multiscale_epe_forward (same
+ * shape limits, same workspace).  The 'hard' mode (top-k of the error map, :268-324) is not a fused kernel: the host
+ * side selects on the per-pixel errors. */
+FN2_API int fn2_multiscale_epe_edges_forward(const float* flow, float flow_scale, const float* const* predictions,
+                                     const float* const* edges, float lambda_w, const int* out_hw, int num_scales,
+                                     int N, int in_h, int in_w, int C, float* const* downsampled,
+                                     float* const* residual_dir, float* epe_sums, void* workspace,
+                                     size_t workspace_bytes, void* stream);
 
 /* 1 if fn2_multiscale_epe_forward takes these shapes, 0 if it would answer FN2_E_UNSUPPORTED_GEOMETRY (limits above),
  * or a negative fn2_status for arguments the downsample op itself rejects.  Host-only: no CUDA call is made. */

@@ -204,3 +204,42 @@ def test_tie_case_half_of_the_window_nan():
     want = o.c_downsample(x.numpy(), (9, 9))
     assert (np.isnan(out) == np.isnan(want)).all()
     assert_close(out, want, rel=1e-5, abs_=5e-6, what="tie case")
+
+
+# ---- HFEM 'edges' weighting in the fused pass: fn2_multiscale_epe_edges_forward ------------------------------------
+@pytest.mark.parametrize("shape,sizes,lam", [
+    ((3, 384, 512, 2), LOSS_SIZES, 2.0),                        # the fused kernels
+    ((2, 96, 128, 2), [(6, 8), (12, 16), (24, 32)], 0.5),
+    ((1, 436, 1024, 2), [(7, 16), (14, 32), (28, 64)], 2.0),    # wider than the fused kernels take: unfused nodes
+])
+def test_multiscale_epe_with_edge_weights(shape, sizes, lam):
+    """epe[s] = sum(epe_s + lambda * epe_s * downsample(edges, size_s)) / N (utils.py:326-334 on the per-scale edge
+    maps of flownet_s_interp.py:177-233) against float64 on the oracle's downsampled tensors; gradient w.r.t. the
+    predictions against autograd through the same formula."""
+    N, H, W, C = shape
+    x = _input(*shape, seed=31, nan=False)
+    g = torch.Generator().manual_seed(32)
+    edges = torch.rand(N, H, W, 1, generator=g)
+    preds = [torch.randn(N, h, w, C, generator=g) for h, w in sizes]
+    xs = (x.numpy() * np.float32(0.05)).astype(np.float32)
+    want = []
+    for p in preds:
+        size = (p.shape[1], p.shape[2])
+        d = o.c_downsample(xs, size).astype(np.float64)
+        e = o.c_downsample(edges.numpy(), size).astype(np.float64)
+        epe = np.sqrt(((p.numpy().astype(np.float64) - d) ** 2).sum(3, keepdims=True))
+        want.append((epe + lam * epe * e).sum() / N)
+    pd = [p.cuda().requires_grad_() for p in preds]
+    epe, downs = fn2.multiscale_epe(x.cuda(), pd, 0.05, return_downsampled=True, edges=edges.cuda(), lambda_w=lam)
+    np.testing.assert_allclose(epe.detach().cpu().numpy(), want, rtol=2e-5)
+    plain = fn2.multiscale_epe(x.cuda(), [p.detach() for p in pd], 0.05)
+    assert (epe.detach() > plain).all()                         # the weighting is on
+    emaps = fn2.downsample_multi(edges.cuda(), sizes)
+    epe.sum().backward()
+    for p, d, e in zip(pd, downs, emaps):
+        q = p.detach().clone().requires_grad_()
+        m = torch.sqrt(((q - d) ** 2).sum(3, keepdim=True))
+        ((m + lam * (m * e)).sum() / N).backward()
+        torch.testing.assert_close(p.grad, q.grad, rtol=1e-5, atol=1e-9)
+    with pytest.raises(ValueError):
+        fn2.multiscale_epe(x.cuda(), [p.detach() for p in pd], 0.05, edges=edges[:, :-1].cuda())

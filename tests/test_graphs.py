@@ -112,6 +112,42 @@ def test_loss_matches_a_direct_restatement():
     assert len(parts) == 5
 
 
+def test_hfem_losses_match_a_numpy_restatement():
+    """average_endpoint_error_hfem (utils.py:227-339) in its three modes and the multi-scale loss built on it
+    (flownet_s_interp.py:160-245), against float64 numpy written from the formulas."""
+    ops = oracle_ops()
+    g = torch.Generator().manual_seed(16)
+    gt = torch.randn(2, 64, 64, 2, generator=g) * 4
+    edges = torch.rand(2, 64, 64, 1, generator=g)
+    sides = (2, 2, 4, 8, 16)
+    preds = {"predict_flow%d" % k: torch.randn(2, n, n, 2, generator=g) for k, n in zip((6, 5, 4, 3, 2), sides)}
+    lam, perc = 2.0, 50
+    for mode in ("edges", "hard", ""):
+        total, parts = G.multiscale_loss_hfem(gt, preds, ops, add_hfem=mode, lambda_w=lam, perc_hfem=perc, edges=edges)
+        want = []
+        for k in (6, 5, 4, 3, 2):
+            p = preds["predict_flow%d" % k].numpy().astype(np.float64)
+            size = [p.shape[1], p.shape[2]]
+            d = ops.downsample(gt * 0.05, size).numpy().astype(np.float64)
+            epe = np.sqrt(((p - d) ** 2).sum(3, keepdims=True))
+            if mode == "edges":
+                e = ops.downsample(edges, size).numpy().astype(np.float64)
+                want.append((epe + lam * epe * e).sum() / 2)
+            elif mode == "hard":
+                flat = np.sort(epe.reshape(-1))[::-1]
+                kk = int(round(perc / 100 * flat.size))
+                want.append((1 + lam) * flat[:kk].sum() / 2 * flat.size / kk)
+            else:
+                want.append(epe.sum() / 2)
+        np.testing.assert_allclose([float(x) for x in parts], want, rtol=2e-5)
+        wsum = sum(w * l for w, l in zip((0.32, 0.08, 0.02, 0.01, 0.005), want)) / 5
+        assert abs(float(total) - wsum) < 1e-4 * max(1.0, abs(wsum))
+    # 'edges' without an edge map is the plain loss (utils.py:335-337)
+    a, _ = G.multiscale_loss_hfem(gt, preds, ops, add_hfem="edges", edges=None)
+    b, _ = G.multiscale_loss(gt, preds, ops)
+    assert float(a) == float(b)
+
+
 def test_weighted_loss_is_pinned_to_a_hand_computed_compute_weighted_loss():
     """tf.losses.compute_weighted_loss(losses, weights) = sum(losses * weights) / count(weights != 0): for losses
     10, 20, 30, 40, 50 and the FlowNet weights that is (3.2 + 1.6 + 0.6 + 0.4 + 0.25) / 5 = 1.21, not 6.05."""
